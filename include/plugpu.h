@@ -1,0 +1,233 @@
+/*
+ * plugpu.h — C ABI of libplugpu.so, the B200-native render path for andrew-pa/plutracer.
+ *
+ * This is the drop-in boundary: everything the reference does between
+ *     plu::renderer r(scene, cam, tile, sampler, lights);  r.render(target);
+ * (reference src/main.cpp:171,177  ->  src/renderer.cpp:98-150 render, :59-96 ray_color,
+ *  :5-57 estimate_direct_light / uniform_sample_one_light) happens behind these entry points.
+ * Host code (the reference's own C++ via integration/plu_gpu_renderer.h, or this repo's .urn
+ * loader) flattens the loaded scene into the POD tables below and calls in; there are no C++
+ * or torch types in any signature.  No exceptions cross the boundary: every call returns
+ * PLU_OK (0) or a negative PLU_E_* code, and plu_gpu_last_error() gives the message
+ * (the reference throws runtime_error / bare `throw;`, surface.h:17,21, scene.h:90-123).
+ *
+ * There is NO CPU fallback: calls that need the GPU return PLU_E_CUDA when no device is usable.
+ */
+#ifndef PLUGPU_H
+#define PLUGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PLUGPU_ABI_VERSION 1
+
+/* ---- error codes ------------------------------------------------------------------------- */
+enum {
+	PLU_OK          =  0,
+	PLU_E_ARG       = -1,  /* bad argument / malformed table                                   */
+	PLU_E_CUDA      = -2,  /* CUDA runtime error (message names the call)                      */
+	PLU_E_NOSCENE   = -3,  /* render / trace before plu_gpu_upload_scene                       */
+	PLU_E_IO        = -4,  /* file could not be read / written                                 */
+	PLU_E_PARSE     = -5,  /* .urn / OBJ / BMP syntax or semantic error                        */
+	PLU_E_NOMEM     = -6
+};
+
+/* ---- tags (virtual dispatch in the reference -> tag-indexed device tables) ---------------- */
+enum { /* surface kinds: reference inc/surfaces/{sphere,box,triangle}.h                        */
+	PLU_PRIM_SPHERE   = 0, /* data: cx cy cz r                                                 */
+	PLU_PRIM_BOX      = 1, /* data: min.xyz 0 | max.xyz 0          (box_bounds, box.h:7)       */
+	PLU_PRIM_TRIANGLE = 2  /* data: v0.xyz 0 | v1.xyz 0 | v2.xyz 0 (triangle.h:7-9)            */
+};
+enum { /* material kinds: reference inc/material.h:213-254, inc/lights/area_light.h:45-56       */
+	PLU_MAT_DIFFUSE            = 0, /* color                                                   */
+	PLU_MAT_PERFECT_REFLECTION = 1, /* color, p0 = eta (vec3), p1 = k (vec3)                    */
+	PLU_MAT_PERFECT_REFRACTION = 2, /* color, p0[0] = eta_t, p0[1] = eta_i (ctor order, :236)   */
+	PLU_MAT_GLASS              = 3, /* color, p0[0] = ior                                      */
+	PLU_MAT_EMISSION           = 4  /* light = index of its diffuse_area_light                  */
+};
+enum { /* texture kinds: reference inc/textures/textures.h, inc/texture.h:53-60                  */
+	PLU_TEX_CHECKERBOARD = 0,  /* c0 = colors[0], c1 = colors[1], scale                          */
+	PLU_TEX_GRID         = 1,  /* c0 = fg_color, c1 = bg_color (ctor order :25), scale, line     */
+	PLU_TEX_IMAGE        = 2   /* img_w, img_h, img_offset into image_texels (rgb float)         */
+};
+enum { /* light kinds: reference inc/light.h:15-35, inc/lights/area_light.h:12-43                */
+	PLU_LIGHT_POINT        = 0, /* a = pos, b = intensity                                       */
+	PLU_LIGHT_DIFFUSE_AREA = 1  /* b = Lemit, prim = index of its surface, area = surf->area()  */
+};
+
+/* ---- flat scene tables -------------------------------------------------------------------- */
+typedef struct plu_camera_desc {   /* public fields of plu::camera, reference inc/camera.h:9-14   */
+	float pos[3];
+	float look[3];
+	float up[3];
+	float right[3];
+	float inv_image_size[2];       /* 1/(W,H) the camera was BUILT for (scene resolution)        */
+	float w;
+	float lens_radius;
+	float focal_distance;
+} plu_camera_desc;
+
+typedef struct plu_material_desc {
+	int32_t tag;          /* PLU_MAT_*                                                          */
+	int32_t texture;      /* index into textures, or -1: constant `color` (props.h:24-30)       */
+	int32_t light;        /* PLU_MAT_EMISSION: index into lights; else -1                       */
+	int32_t reserved;
+	float   color[3];
+	float   p0[3];
+	float   p1[3];
+} plu_material_desc;
+
+typedef struct plu_texture_desc {
+	int32_t tag;          /* PLU_TEX_*                                                          */
+	int32_t img_w, img_h; /* image only                                                         */
+	int32_t img_offset;   /* first texel (in texels, not floats) inside image_texels            */
+	float   c0[3];
+	float   c1[3];
+	float   scale;
+	float   line;
+} plu_texture_desc;
+
+typedef struct plu_light_desc {
+	int32_t tag;          /* PLU_LIGHT_*                                                        */
+	int32_t prim;         /* area light: index of the emitting surface in the prim table        */
+	float   a[3];         /* point: pos                                                         */
+	float   b[3];         /* point: intensity; area: Lemit                                      */
+	float   area;         /* area light: surf->area() as the reference computes it (quirks in)  */
+	float   reserved;
+} plu_light_desc;
+
+/*
+ * The whole scene.  All pointers are HOST pointers borrowed for the duration of the call.
+ * Surface ids everywhere in this ABI = index into the prim table = position in
+ * plu::scenes::scene::surfs in LOAD order, captured before bvh_tree sorts it in place
+ * (reference src/surfaces/bvh_tree.cpp:23).
+ */
+typedef struct plu_scene_desc {
+	uint32_t abi_version;               /* PLUGPU_ABI_VERSION                                   */
+	uint32_t reserved0;
+	plu_camera_desc cam;
+	int32_t  n_prims;
+	int32_t  n_materials;
+	int32_t  n_textures;
+	int32_t  n_lights;
+	const int32_t* prim_tag;            /* [n_prims] PLU_PRIM_*                                 */
+	const int32_t* prim_material;       /* [n_prims] index into materials                       */
+	const float*   prim_data;           /* [n_prims*12] three float4 per prim, see PLU_PRIM_*   */
+	const float*   prim_tri_uv;         /* [n_prims*6]  triangle texture_coords[0..2], or NULL  */
+	const float*   prim_tri_normal;     /* [n_prims*9]  triangle normals[0..2], or NULL         */
+	const plu_material_desc* materials;
+	const plu_texture_desc*  textures;
+	const plu_light_desc*    lights;    /* order = plu::scenes::scene::lights                   */
+	const float*   image_texels;        /* rgb float, all image textures back to back, or NULL  */
+	int64_t  n_image_texels;
+	const int32_t* prim_tie_rank;       /* [n_prims] or NULL.  Rank of each surface among the
+	                                       leaves of the reference bvh_tree in DFS (left first)
+	                                       order; equal-t hits resolve to the HIGHER rank
+	                                       (bvh_tree.cpp:73).  NULL: the library restates the
+	                                       reference build (bvh_tree.cpp:7-36) to derive it.    */
+} plu_scene_desc;
+
+/* ---- render call -------------------------------------------------------------------------- */
+enum { /* plu_render_params.flags                                                                */
+	PLU_RENDER_COMPAT_OVERFLOW_COLUMN = 1u << 0, /* reproduce sampler.h:74-89: the x==W strip is
+	                                                rendered and lands in pixel (0,y+1)          */
+	PLU_RENDER_BVH_REFERENCE          = 1u << 1, /* traverse the reference's own tree literally
+	                                                (origin-inflated bounds, both children, no
+	                                                early-out) — verification mode               */
+	PLU_RENDER_COUNT_BVH              = 1u << 2  /* fill bvh_nodes_visited / prims_tested         */
+};
+
+typedef struct plu_render_params {
+	int32_t  width, height;        /* target->size (texture.h:32)                               */
+	int32_t  n_strata;             /* sampler->sample_count.x (== .y); spp = n_strata^2         */
+	int32_t  max_vertices;         /* 8 = the reference (renderer.cpp:83 `bounces > 6`)         */
+	uint64_t seed;                 /* Philox key                                                */
+	uint32_t flags;
+	int32_t  sample_begin;         /* this call renders sample indices                          */
+	int32_t  sample_stride;        /*   s = sample_begin + k*sample_stride, k < sample_count    */
+	int32_t  sample_count;         /*   (0 -> all n_strata^2: begin 0, stride 1)                */
+	int32_t  strata_per_wave;      /* paths in flight = W*H*this; 0 -> library picks             */
+	int32_t  reserved;
+} plu_render_params;
+
+typedef struct plu_render_stats {
+	uint64_t samples;              /* ray_color calls (paths)                                   */
+	uint64_t rays_extend;          /* closest-hit queries from the path loop                    */
+	uint64_t rays_shadow;          /* light-sample + BSDF-MIS connection rays                   */
+	uint64_t bvh_nodes_visited;    /* PLU_RENDER_COUNT_BVH only                                 */
+	uint64_t prims_tested;         /* PLU_RENDER_COUNT_BVH only                                 */
+	double   ms_device;            /* CUDA-event time of the whole render on its stream         */
+	double   ms_extend;            /* per-stage CUDA-event sums (0 unless profiling flag)       */
+	double   ms_shade;
+	double   ms_connect;
+	uint64_t kernel_launches;      /* kernels this call launched                                */
+} plu_render_stats;
+
+typedef struct plu_gpu_ctx plu_gpu_ctx;
+
+/* Create a context on CUDA device `device` (one process / context per GPU).                     */
+int  plu_gpu_create(int device, plu_gpu_ctx** out);
+void plu_gpu_destroy(plu_gpu_ctx* ctx);
+/* Message of the last failing call on ctx (ctx may be NULL: last plu_gpu_create failure).       */
+const char* plu_gpu_last_error(const plu_gpu_ctx* ctx);
+
+/* Deep-copy the tables to the device, build the traversal structure.  Replaces scene->hit,
+ * the material/light/texture object graphs and bvh_tree construction (main.cpp:168-171).        */
+int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* scene);
+
+/* renderer::render (renderer.cpp:98-150): out_rgb is target->_pixels, HOST, W*H*3 float,
+ * row-major y down (texture.h:40-47), ACCUMULATED INTO (+=) like the reference.  Blocks.      */
+int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, float* out_rgb,
+                   plu_render_stats* stats);
+
+/* Same, but d_rgb is a DEVICE pointer on ctx's device and the work is enqueued on `stream`
+ * (a cudaStream_t, NULL = the context's own stream) — used for multi-GPU so the per-GPU
+ * framebuffers can be combined by one NCCL reduce.  Synchronises `stream` before returning.    */
+int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb,
+                          void* stream, plu_render_stats* stats);
+
+/* Parity hooks.  Pixel-centre pinhole rays through camera::generate_ray (camera.h:25-37) then
+ * scene->hit: per pixel the hit surface id (-1 = miss), t, and hit_record::norm.               */
+int plu_gpu_trace_primary(plu_gpu_ctx* ctx, int32_t width, int32_t height, uint32_t flags,
+                          int32_t* surf_id, float* t, float* normal3);
+/* Arbitrary rays (o,d each n*3 float) through scene->hit.                                      */
+int plu_gpu_trace_rays(plu_gpu_ctx* ctx, int64_t n, const float* origin3, const float* dir3,
+                       uint32_t flags, int32_t* surf_id, float* t, float* normal3);
+/* Per-sample radiance of ray_color for samples [sample_begin, +sample_count) of the pixels
+ * [pixel_begin, +pixel_count) (row-major index): out_rgb[(p*sample_count+s)*3].  Lets tests
+ * compare single paths with the oracle driven by the same Philox stream.                       */
+int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params* p, int64_t pixel_begin,
+                            int64_t pixel_count, float* out_rgb);
+
+/* ---- host-side scene plumbing (no GPU needed) --------------------------------------------- */
+typedef struct plu_scene plu_scene;   /* owns the arrays a plu_scene_desc points at              */
+
+/* Load a .urn scene the way plu::scenes::scene does (scene.h:229-298).  args = the reference
+ * CLI overrides ("/res", "640x480", "/smp", "4").  Replaces urn::value + scenes::scene.       */
+int plu_scene_load_urn(const char* path, const char* const* args, int n_args,
+                       plu_scene** out, char* err, int err_len);
+/* Flat binary form of a plu_scene_desc (".pluscene"), for fixtures and caching.                */
+int plu_scene_load_flat(const char* path, plu_scene** out, char* err, int err_len);
+int plu_scene_save_flat(const plu_scene_desc* desc, int32_t width, int32_t height,
+                        int32_t n_strata, const char* path);
+/* Wrap/deep-copy an existing desc (e.g. produced by the integration adapter).                  */
+int plu_scene_from_desc(const plu_scene_desc* desc, int32_t width, int32_t height,
+                        int32_t n_strata, plu_scene** out);
+const plu_scene_desc* plu_scene_get_desc(const plu_scene* s);
+void plu_scene_get_defaults(const plu_scene* s, int32_t* width, int32_t* height,
+                            int32_t* n_strata);  /* resolution / antialiasing-samples           */
+void plu_scene_free(plu_scene* s);
+
+/* Restatement of the reference BVH build order (bvh_tree.cpp:7-36): fills rank[n_prims] with
+ * each surface's position among the leaves in DFS order.  Exposed for tests.                   */
+int plu_scene_reference_leaf_order(const plu_scene_desc* desc, int32_t* rank);
+
+uint32_t plu_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLUGPU_H */
