@@ -137,7 +137,11 @@ enum { /* plu_render_params.flags                                               
 	PLU_RENDER_BVH_REFERENCE          = 1u << 1, /* traverse the reference's own tree literally
 	                                                (origin-inflated bounds, both children, no
 	                                                early-out) — verification mode               */
-	PLU_RENDER_COUNT_BVH              = 1u << 2  /* fill bvh_nodes_visited / prims_tested         */
+	PLU_RENDER_COUNT_BVH              = 1u << 2, /* fill bvh_nodes_visited / prims_tested         */
+	PLU_RENDER_BVH_FAST               = 1u << 3, /* use the tight SAH BVH even for a small scene
+	                                                (default: scenes with > 64 surfaces)         */
+	PLU_RENDER_PROFILE                = 1u << 4  /* CUDA events between all launches: fills
+	                                                ms_generate/extend/shade/connect/accumulate   */
 };
 
 typedef struct plu_render_params {
@@ -160,10 +164,14 @@ typedef struct plu_render_stats {
 	uint64_t bvh_nodes_visited;    /* PLU_RENDER_COUNT_BVH only                                 */
 	uint64_t prims_tested;         /* PLU_RENDER_COUNT_BVH only                                 */
 	double   ms_device;            /* CUDA-event time of the whole render on its stream         */
-	double   ms_extend;            /* per-stage CUDA-event sums (0 unless profiling flag)       */
+	double   ms_extend;            /* per-stage CUDA-event sums (PLU_RENDER_PROFILE only)       */
 	double   ms_shade;
 	double   ms_connect;
 	uint64_t kernel_launches;      /* kernels this call launched                                */
+	double   ms_generate;
+	double   ms_accumulate;
+	uint64_t shade_vertices;       /* path vertices shaded (= extension rays that hit)          */
+	uint64_t shadow_entries;       /* shaded vertices that needed a connection                  */
 } plu_render_stats;
 
 typedef struct plu_gpu_ctx plu_gpu_ctx;
@@ -219,6 +227,10 @@ int plu_scene_from_desc(const plu_scene_desc* desc, int32_t width, int32_t heigh
 const plu_scene_desc* plu_scene_get_desc(const plu_scene* s);
 void plu_scene_get_defaults(const plu_scene* s, int32_t* width, int32_t* height,
                             int32_t* n_strata);  /* resolution / antialiasing-samples           */
+/* The reference CLI overrides applied after loading: "/res WxH" rebuilds the camera's
+ * inv_image_size = 1/(W,H) (scene.h:232-248, camera.h:18) and "/smp N" replaces
+ * antialiasing-samples (scene.h:251-256).  A value <= 0 leaves that setting alone.              */
+int plu_scene_override(plu_scene* s, int32_t width, int32_t height, int32_t n_strata);
 void plu_scene_free(plu_scene* s);
 
 /* Restatement of the reference BVH build order (bvh_tree.cpp:7-36): fills rank[n_prims] with

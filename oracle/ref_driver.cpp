@@ -14,6 +14,7 @@
 //   plu_ref render     <scene.urn> <W> <H> <smp> <out.bin>      renderer::render (its own threads)
 //   plu_ref render-st  <scene.urn> <W> <H> <smp> <seed> <out.bin> [x0 y0 x1 y1 [samples.bin]]
 //                                                               1 thread, RNG reseeded per pixel
+//   plu_ref render-flat <scene.pluscene> <W> <H> <smp> <out.bin|->  renderer::render on a scene rebuilt from flat tables
 //   plu_ref dump-scene <scene.urn> <W> <H> <smp> <out.pluscene> flat tables via the integration adapter
 //   plu_ref leaf-order <scene.urn>                              load-order ids of the bvh leaves in DFS order
 #include "cmmn.h"
@@ -68,6 +69,75 @@ void load(loaded& L, const std::string& path, int W, int H, int smp) {
 	L.sc.reset(new plu::scenes::scene(tlv, args));
 	for (auto& s : L.sc->surfs) { L.id_of[s.get()] = (int32_t)L.load_order.size(); L.load_order.push_back(s.get()); }
 	L.tree.reset(new plu::surfaces::bvh_tree(L.sc->surfs));  // sorts sc->surfs in place (bvh_tree.cpp:23)
+}
+
+// Rebuild the reference's OWN object graph (its sphere / box / material / light classes) from a flat
+// ".pluscene" fixture, so the unmodified renderer can run where the .urn files are not available (the
+// GPU box has no /root/reference).  Inverse of integration/plu_gpu_renderer.h's flattener.
+struct flat_loaded {
+	plu::camera cam;
+	std::vector<std::shared_ptr<plu::surface>> surfs;
+	std::vector<std::shared_ptr<plu::light>> lights;
+	int samples = 0; int W = 0, H = 0;
+	std::unique_ptr<plu::surfaces::bvh_tree> tree;
+};
+
+glm::vec3 v3of(const float* f) { return glm::vec3(f[0], f[1], f[2]); }
+
+void load_flat(flat_loaded& L, const std::string& path, int W, int H, int smp) {
+	plu_scene* ps = nullptr; char err[256];
+	if (plu_scene_load_flat(path.c_str(), &ps, err, sizeof(err)) != PLU_OK) throw std::runtime_error(err);
+	if (W > 0 || smp > 0) plu_scene_override(ps, W, H, smp);
+	const plu_scene_desc* d = plu_scene_get_desc(ps);
+	int32_t w, h, n; plu_scene_get_defaults(ps, &w, &h, &n);
+	L.W = w; L.H = h; L.samples = n;
+	L.cam.pos = v3of(d->cam.pos); L.cam.look = v3of(d->cam.look); L.cam.up = v3of(d->cam.up); L.cam.right = v3of(d->cam.right);
+	L.cam.inv_image_size = glm::vec2(d->cam.inv_image_size[0], d->cam.inv_image_size[1]);
+	L.cam.w = d->cam.w; L.cam.lens_radius = d->cam.lens_radius; L.cam.focal_distance = d->cam.focal_distance;
+	auto color_of = [&](const plu_material_desc& m) -> plu::props::color {
+		if (m.texture < 0) return plu::props::color(v3of(m.color));
+		const plu_texture_desc& t = d->textures[m.texture];
+		if (t.tag == PLU_TEX_CHECKERBOARD) return plu::props::color(std::make_shared<plu::textures::checkerboard_texture>(v3of(t.c0), v3of(t.c1), t.scale));
+		if (t.tag == PLU_TEX_GRID) return plu::props::color(std::make_shared<plu::textures::grid_texture>(v3of(t.c0), v3of(t.c1), t.scale, t.line));
+		throw std::runtime_error("render-flat: image textures are not rebuilt");
+	};
+	std::vector<std::shared_ptr<plu::material>> mats((size_t)d->n_materials);
+	std::vector<std::shared_ptr<plu::materials::emission_material>> emis((size_t)d->n_materials);
+	for (int32_t i = 0; i < d->n_materials; ++i) {
+		const plu_material_desc& m = d->materials[i];
+		switch (m.tag) {
+			case PLU_MAT_DIFFUSE: mats[i] = std::make_shared<plu::materials::diffuse_material>(color_of(m)); break;
+			case PLU_MAT_PERFECT_REFLECTION: mats[i] = std::make_shared<plu::materials::perfect_reflection_material>(color_of(m), v3of(m.p0), v3of(m.p1)); break;
+			case PLU_MAT_PERFECT_REFRACTION: mats[i] = std::make_shared<plu::materials::perfect_refraction_material>(color_of(m), m.p0[0], m.p0[1]); break;
+			case PLU_MAT_GLASS: mats[i] = std::make_shared<plu::materials::glass_material>(color_of(m), m.p0[0]); break;
+			default: emis[i] = std::make_shared<plu::materials::emission_material>(nullptr); mats[i] = emis[i]; break;
+		}
+	}
+	for (int32_t s = 0; s < d->n_prims; ++s) {
+		const float* f = d->prim_data + (size_t)s * 12;
+		std::shared_ptr<plu::surface> surf;
+		if (d->prim_tag[s] == PLU_PRIM_SPHERE) surf = std::make_shared<plu::surfaces::sphere>(v3of(f), f[3], nullptr);
+		else if (d->prim_tag[s] == PLU_PRIM_BOX) {
+			auto b = std::make_shared<plu::surfaces::box>(glm::vec3(0.f), glm::vec3(0.f), nullptr);
+			b->box_bounds._min = v3of(f); b->box_bounds._max = v3of(f + 4);   // exact bits, not c -+ e again
+			surf = b;
+		} else throw std::runtime_error("render-flat: triangle meshes are not rebuilt");
+		surf->mat = mats[(size_t)d->prim_material[s]];
+		L.surfs.push_back(surf);
+	}
+	L.lights.resize((size_t)d->n_lights);
+	for (int32_t i = 0; i < d->n_lights; ++i) {
+		const plu_light_desc& l = d->lights[i];
+		if (l.tag == PLU_LIGHT_POINT) L.lights[i] = std::make_shared<plu::lights::point_light>(v3of(l.a), v3of(l.b));
+		else {
+			auto al = std::make_shared<plu::lights::diffuse_area_light>(v3of(l.b), L.surfs[(size_t)l.prim]);   // area = surf->area()
+			for (int32_t m = 0; m < d->n_materials; ++m) if (d->materials[m].tag == PLU_MAT_EMISSION && d->materials[m].light == i) emis[m]->L = al;
+			L.lights[i] = al;
+		}
+	}
+	plu_scene_free(ps);
+	std::vector<std::shared_ptr<plu::surface>> sorted = L.surfs;   // bvh_tree sorts its argument in place (bvh_tree.cpp:23)
+	L.tree.reset(new plu::surfaces::bvh_tree(sorted));
 }
 
 void write_all(const std::string& path, const void* p, size_t bytes, bool append = false) {
@@ -139,6 +209,22 @@ int main(int argc, char** argv) {
 			double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
 			printf("{\"mode\": \"render\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f, \"threads\": %u}\n",
 			       W, H, smp, (unsigned long long)W * H * smp * smp, ms, std::thread::hardware_concurrency());
+		} else if (mode == "render-flat" && argc == 7) {
+			// renderer::render of the unmodified reference on a scene rebuilt from a .pluscene fixture
+			int W = atoi(argv[3]), H = atoi(argv[4]), smp = atoi(argv[5]);
+			flat_loaded L; load_flat(L, scene_path, W, H, smp);
+			auto tx = std::make_shared<padded_target>(glm::uvec2(L.W, L.H));
+			plu::samplers::stratified_sampler sampler(tx->size, glm::uvec2((unsigned)L.samples), true);
+			plu::renderer r(L.tree.get(), L.cam, glm::uvec2(32), &sampler, L.lights);
+			std::streambuf* old = std::cout.rdbuf(); std::ostringstream sink; std::cout.rdbuf(sink.rdbuf());
+			auto t0 = std::chrono::high_resolution_clock::now();
+			r.render(tx);
+			auto t1 = std::chrono::high_resolution_clock::now();
+			std::cout.rdbuf(old);
+			if (std::string(argv[6]) != "-") write_all(argv[6], &tx->pixel(glm::uvec2(0, 0)), (size_t)L.W * L.H * 12);
+			double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+			printf("{\"mode\": \"render-flat\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f, \"threads\": %u}\n",
+			       L.W, L.H, L.samples, (unsigned long long)L.W * L.H * L.samples * L.samples, ms, std::thread::hardware_concurrency());
 		} else if (mode == "render-st" && (argc == 8 || argc == 12 || argc == 13)) {
 			int W = atoi(argv[3]), H = atoi(argv[4]), smp = atoi(argv[5]);
 			unsigned long seed = strtoul(argv[6], nullptr, 10);

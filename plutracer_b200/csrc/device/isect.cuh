@@ -1,0 +1,249 @@
+// isect.cuh — primitive intersection and BVH traversal (replaces scene->hit: bvh_tree.cpp:39-76,
+// aabb::hit cmmn.h:151-173, sphere.cpp:16-47, box.cpp:6-62, triangle.cpp:5-33).
+//
+// Traversal only decides (t, surface); the rest of hit_record (norm, uv, dpdu) is a pure function of
+// (ray, t, surface) and is rebuilt by the consumer with fill_record(), so a hit travels between
+// kernels as 8 bytes instead of the reference's 56-byte record.
+#pragma once
+#include "scene_dev.cuh"
+
+namespace plud {
+
+struct ray { f3 e, d; };
+PLU_DEV f3 ray_at(const ray& r, float t) { return r.e + r.d * t; }
+
+#define PLU_T_MAX 100000.f   // hit_record::t initial value, cmmn.h:229
+
+struct hit_rec {   // what shading needs of hit_record (dpdv is never read by the path)
+	f3 norm; f2 uv; f3 dpdu;
+};
+
+// aabb::hit / box::hit slab arithmetic, cmmn.h:155-169 == box.cpp:8-23
+PLU_DEV void slabs(f3 mn, f3 mx, const ray& r, float& tmin, float& tmax) {
+	f3 rrd = 1.f / r.d;
+	f3 t1 = (mn - r.e) * rrd;
+	f3 t2 = (mx - r.e) * rrd;
+	f3 m12 = mk3(gmin(t1.x, t2.x), gmin(t1.y, t2.y), gmin(t1.z, t2.z));
+	f3 x12 = mk3(gmax(t1.x, t2.x), gmax(t1.y, t2.y), gmax(t1.z, t2.z));
+	tmin = m12.x; tmin = gmax(tmin, m12.y); tmin = gmax(tmin, m12.z);
+	tmax = x12.x; tmax = gmin(tmax, x12.y); tmax = gmin(tmax, x12.z);
+}
+
+// t-only versions of surface::hit(r, hr) with hr->t == bound on entry.
+PLU_DEV bool sphere_t(float4 cr, const ray& r, float bound, float& t) {   // sphere.cpp:17-26
+	f3 v = r.e - mk3(cr);
+	float b = -dot(v, r.d);
+	float det = (b * b) - dot(v, v) + cr.w * cr.w;
+	if (det < 0) return false;
+	det = sqrtf(det);
+	float i1 = b - det, i2 = b + det;
+	if (i2 > 0 && i1 > 0) {
+		if (bound < i1) return false;
+		t = i1; return true;
+	}
+	return false;
+}
+PLU_DEV bool box_t(float4 mn, float4 mx, const ray& r, float bound, float& t) {   // box.cpp:8-27
+	float tmin, tmax; slabs(mk3(mn), mk3(mx), r, tmin, tmax);
+	if (tmax < tmin || tmin < 0) return false;
+	if (tmin > bound) return false;
+	t = tmin; return true;
+}
+PLU_DEV bool triangle_t(float4 a, float4 b, float4 c, const ray& r, float bound, float& t) {   // triangle.cpp:6-25
+	f3 v0 = mk3(a);
+	f3 e1 = mk3(b) - v0, e2 = mk3(c) - v0;
+	f3 pv = cross(r.d, e2);
+	float det = dot(e1, pv);
+	if (det == 0) return false;
+	float idet = 1.f / det;
+	f3 tv = r.e - v0;
+	float u = dot(tv, pv) * idet;
+	if (u < 0 || u > 1.f) return false;
+	f3 qv = cross(tv, e1);
+	float v = dot(r.d, qv) * idet;
+	if (v < 0 || u + v > 1) return false;
+	float nt = dot(e2, qv) * idet;
+	if (nt > 0 && nt < bound) { t = nt; return true; }
+	return false;
+}
+
+PLU_DEV bool prim_t(const scene_ref& sc, int32_t s, int32_t tag, const ray& r, float bound, float& t) {
+	const float4* p = sc.prim(s);
+	if (tag == PLU_PRIM_BOX) return box_t(p[0], p[1], r, bound, t);
+	if (tag == PLU_PRIM_SPHERE) return sphere_t(p[0], r, bound, t);
+	return triangle_t(p[0], p[1], p[2], r, bound, t);
+}
+
+// box::get_normal, box.cpp:37-62
+PLU_DEV f3 box_normal(f3 mn, f3 mx, f3 p) {
+	f3 c = (mn + mx) * 1.f / 2.f;
+	f3 ext = mx - c;
+	f3 n = mk3(0.f);
+	float m = 3.402823466e+38f;
+	f3 np = p - c;
+#pragma unroll
+	for (int i = 0; i < 3; ++i) {
+		float dist = fabsf(comp(ext, i) - fabsf(comp(np, i)));
+		if (dist < m) {
+			m = dist;
+			float sg = gsign(comp(np, i));
+			n = mk3(sg * (i == 0 ? 1.f : 0.f), sg * (i == 1 ? 1.f : 0.f), sg * (i == 2 ? 1.f : 0.f));
+		}
+	}
+	return n;
+}
+
+// The remaining fields of hit_record for a hit of surface s at distance t along r.
+// want_uv: the material is textured (sphere uv costs two acos + a sin).
+PLU_DEV void fill_record(const scene_ref& sc, int32_t s, int32_t tag, const ray& r, float t, bool want_uv, hit_rec& hr) {
+	const float4* p = sc.prim(s);
+	hr.uv = mk2(0.f, 0.f);
+	if (tag == PLU_PRIM_BOX) {   // box.cpp:28-34
+		f3 q = ray_at(r, t);
+		f3 n = box_normal(mk3(p[0]), mk3(p[1]), q);
+		uint32_t mci = 0;
+		if (n.x != 0.f) mci = 0; if (n.y != 0.f) mci = 1; if (n.z != 0.f) mci = 2;
+		uint32_t ia = (mci - 1u) % 3u, ib = (mci + 1u) % 3u;   // unsigned wraparound, box.cpp:31-33
+		hr.norm = n;
+		hr.uv = mk2(comp(q, (int)ia), comp(q, (int)ib));
+		hr.dpdu = mk3(ia == 0 ? 1.f : 0.f, ia == 1 ? 1.f : 0.f, ia == 2 ? 1.f : 0.f);
+	} else if (tag == PLU_PRIM_SPHERE) {   // sphere.cpp:27-44
+		float4 cr = p[0];
+		hr.norm = normalize(ray_at(r, t) - mk3(cr));
+		if (want_uv) {
+			float cos_phi = -dot(hr.norm, mk3(0.f, 1.f, 0.f));
+			float phi = det_acos(cos_phi);
+			float sin_phi = det_sin(phi);
+			hr.uv.y = phi * PLU_ONE_OVER_PI;
+			float theta = det_acos(dot(mk3(0.f, 0.f, -1.f), hr.norm) / sin_phi) * PLU_TWO_OVER_PI;
+			if (dot(mk3(1.f, 0.f, 0.f), hr.norm) >= 0) theta = 1.f - theta;
+			hr.uv.x = theta;
+		}
+		f3 q = ray_at(r, t);
+		hr.dpdu = mk3(-2.f * PLU_PI * q.y, 2.f * PLU_PI * q.x, 0.f);
+	} else {   // triangle.cpp:26-31 (u, v recomputed exactly as in triangle_t)
+		f3 v0 = mk3(p[0]);
+		f3 e1 = mk3(p[1]) - v0, e2 = mk3(p[2]) - v0;
+		f3 U = normalize(e1), V = normalize(e2);
+		hr.norm = cross(U, V);
+		hr.dpdu = U;
+		if (want_uv) {
+			f3 pv = cross(r.d, e2);
+			float idet = 1.f / dot(e1, pv);
+			f3 tv = r.e - v0;
+			float u = dot(tv, pv) * idet;
+			f3 qv = cross(tv, e1);
+			float v = dot(r.d, qv) * idet;
+			float w = 1 - (u + v);
+			const float* tc = sc.tri_uv + (size_t)s * 6;
+			hr.uv = mk2(tc[0] * u + tc[2] * v + tc[4] * w, tc[1] * u + tc[3] * v + tc[5] * w);
+		}
+	}
+}
+
+// ---- traversal of the reference's own tree ------------------------------------------------------------
+// Same node set, same inflated bounds, same slab test as bvh_node::hit, therefore the same set of
+// surfaces is tested; leaves are met in DFS (left first) order and a later leaf wins unless the
+// earlier one is strictly nearer — `lhr.t < rhr.t ? lhr : rhr`, bvh_tree.cpp:73.  (No t-culling: the
+// reference gives every child a fresh record.)
+struct trace_counts { uint32_t nodes, prims; };
+
+template <bool COUNT>
+PLU_DEV bool trace_ref(const scene_ref& sc, const ray& r, float root_bound, float& t_out, int32_t& prim_out, trace_counts* tc) {
+	const ref_node* nodes = sc.ref_nodes();
+	int32_t n = sc.n_ref_nodes;
+	float best_t = 0.f; int32_t best = -1;
+	int32_t i = 0;
+	while (i < n) {
+		float4 lo = nodes[i].lo, hi = nodes[i].hi;
+		int32_t prim = __float_as_int(hi.w);
+		if (prim >= 0) {
+			int32_t tag = sc.prim_meta(prim).x;
+			float t;
+			if (COUNT) tc->prims++;
+			// a root that is itself a leaf sees the caller's record (renderer.cpp:60,86 reuses hr)
+			if (prim_t(sc, prim, tag, r, n == 1 ? root_bound : PLU_T_MAX, t)) {
+				if (best < 0 || !(best_t < t)) { best_t = t; best = prim; }
+			}
+			i = i + 1;
+		} else {
+			if (COUNT) tc->nodes++;
+			float tmin, tmax; slabs(mk3(lo), mk3(hi), r, tmin, tmax);
+			i = (tmax >= tmin) ? i + 1 : __float_as_int(lo.w);
+		}
+	}
+	t_out = best_t; prim_out = best;
+	return best >= 0;
+}
+
+// scene->hit: the fast BVH when the scene has one (large scenes), else the reference's own tree.
+// Tight binned-SAH BVH2 (host/bvh_build.cpp), nearest-child-first with a short stack and distance
+// culling.  It must return what the reference's exhaustive walk returns, i.e. the minimum-t hit and,
+// among equal t, the surface that comes LAST in the reference tree's DFS leaf order (tie rank, kept
+// in prim_meta.w).  Exactness argument (DESIGN.md "fast BVH"): primitives are tested with the same
+// arithmetic as the reference (prim_t, bound 1e5); a subtree is skipped only if its PADDED box is
+// missed, lies behind the origin, or starts strictly beyond the best t so far (+ a relative guard
+// band), none of which can hide a primitive hit with t <= best; NaN slabs (origin on a slab plane,
+// d == 0 on that axis) drop out of fminf/fmaxf, i.e. count as "inside".  What it does NOT reproduce is
+// the reference losing a true hit because one of its own origin-inflated ancestor boxes rejects the
+// ray by rounding; tests compare both walks on every named scene and on the synthetic ones.
+template <bool COUNT>
+PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc) {
+	const fast_node* nodes = sc.fast_nodes;
+	const float ix = 1.f / r.d.x, iy = 1.f / r.d.y, iz = 1.f / r.d.z;
+	float best_t = 3.0e38f; int32_t best = -1, best_rank = -1;
+	int32_t stack[128]; int sp = 0;   // host/bvh_build.cpp bounds the tree depth to 60
+	int32_t cur = 0;   // node index >= 0, or leaf ~first
+	int32_t cur_count = 0;
+	if (sc.n_fast_nodes == 0) { t_out = 0.f; prim_out = -1; return false; }
+	for (;;) {
+		if (cur >= 0) {
+			const fast_node* nd = nodes + cur;
+			float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c); int4 d = __ldg(&nd->d);
+			if (COUNT) tc->nodes++;
+			float cull = best_t + fabsf(best_t) * 1e-5f;
+			// child 0: min a.xyz, max (a.w, b.x, b.y);  child 1: min (b.z, b.w, c.x), max c.yzw
+			float t1, t2, n0, f0, n1, f1;
+			t1 = (a.x - r.e.x) * ix; t2 = (a.w - r.e.x) * ix; n0 = fminf(t1, t2); f0 = fmaxf(t1, t2);
+			t1 = (a.y - r.e.y) * iy; t2 = (b.x - r.e.y) * iy; n0 = fmaxf(n0, fminf(t1, t2)); f0 = fminf(f0, fmaxf(t1, t2));
+			t1 = (a.z - r.e.z) * iz; t2 = (b.y - r.e.z) * iz; n0 = fmaxf(n0, fminf(t1, t2)); f0 = fminf(f0, fmaxf(t1, t2));
+			t1 = (b.z - r.e.x) * ix; t2 = (c.y - r.e.x) * ix; n1 = fminf(t1, t2); f1 = fmaxf(t1, t2);
+			t1 = (b.w - r.e.y) * iy; t2 = (c.z - r.e.y) * iy; n1 = fmaxf(n1, fminf(t1, t2)); f1 = fminf(f1, fmaxf(t1, t2));
+			t1 = (c.x - r.e.z) * iz; t2 = (c.w - r.e.z) * iz; n1 = fmaxf(n1, fminf(t1, t2)); f1 = fminf(f1, fmaxf(t1, t2));
+			bool h0 = !(f0 < n0) && !(f0 < 0.f) && !(n0 > cull);
+			bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull);
+			if (h0 && h1) {
+				bool first1 = n1 < n0;   // nearer child first; the other goes on the stack
+				int32_t far_c = first1 ? d.x : d.y, far_n = first1 ? d.z : d.w;
+				stack[sp++] = far_c; stack[sp++] = far_n;
+				cur = first1 ? d.y : d.x; cur_count = first1 ? d.w : d.z;
+				continue;
+			}
+			if (h0) { cur = d.x; cur_count = d.z; continue; }
+			if (h1) { cur = d.y; cur_count = d.w; continue; }
+		} else {
+			int32_t first = ~cur;
+			for (int32_t k = 0; k < cur_count; ++k) {
+				int32_t prim = __ldg(sc.fast_prim_index + first + k);
+				int4 meta = sc.prim_meta(prim);
+				float t;
+				if (COUNT) tc->prims++;
+				if (prim_t(sc, prim, meta.x, r, PLU_T_MAX, t)) {
+					if (best < 0 || t < best_t || (t == best_t && meta.w > best_rank)) { best_t = t; best = prim; best_rank = meta.w; }
+				}
+			}
+		}
+		if (sp == 0) break;
+		cur_count = stack[--sp]; cur = stack[--sp];
+	}
+	t_out = best_t; prim_out = best;
+	return best >= 0;
+}
+
+template <bool COUNT>
+PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc) {
+	if (sc.fast_nodes != nullptr) return trace_fast<COUNT>(sc, r, t, prim, tc);
+	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);
+}
+
+}  // namespace plud

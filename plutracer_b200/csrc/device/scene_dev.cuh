@@ -1,0 +1,60 @@
+// scene_dev.cuh — device-side scene tables (tag-indexed; replaces the reference's virtual
+// surface / material / light / texture object graph).
+//
+// The host packs every table into ONE 16-byte-aligned blob (host/scene_pack.cpp).  Kernels get a
+// `scene_ref` by value (kernel parameter = constant bank, uniform reads) whose pointers address the
+// blob in global memory; when the blob is small (all five named scenes: < 2 KB) each CTA first
+// stages it into shared memory with 128-bit copies and re-bases the pointers, so BVH nodes,
+// primitives, materials and lights are then read from on-chip memory by divergent lanes.
+#pragma once
+#include "pmath.cuh"
+#include "plugpu.h"
+
+namespace plud {
+
+// Reference-topology BVH node (bvh_tree.cpp:7-36), pre-order, stackless:
+//   lo = (min.xyz, skip)   hi = (max.xyz, prim)      prim >= 0: leaf (no bounds test, bvh_tree.cpp:40)
+// `skip` = index of the next node in pre-order that is NOT in this node's subtree.
+struct ref_node { float4 lo, hi; };
+
+// Tight two-child node of the fast BVH (host/bvh_build.cpp), 64 B = four 128-bit loads:
+//   a = (c0.min.xyz, c0.max.x)  b = (c0.max.yz, c1.min.xy)  c = (c1.min.z, c1.max.xyz)
+//   d = (child0, child1, -, -) as int: >= 0 inner node index, < 0 leaf: ~first_prim_slot, count in .z/.w
+struct fast_node { float4 a, b, c; int4 d; };
+
+struct scene_ref {
+	const unsigned char* blob;      // base (global, or shared after staging)
+	uint32_t blob_bytes;
+	uint32_t off_ref_nodes, off_prim, off_prim_meta, off_material, off_texture, off_light;
+	int32_t n_ref_nodes, n_prims, n_materials, n_textures, n_lights;
+	// large / optional tables stay in global memory
+	const float* tri_uv;            // [n_prims*6] or null
+	const float* tri_normal;        // [n_prims*9] or null
+	const float* texels;            // image textures, rgb float
+	const fast_node* fast_nodes;    // null: traverse the reference tree
+	const int32_t* fast_prim_index; // leaf slots -> prim ids
+	int32_t n_fast_nodes;
+	plu_camera_desc cam;
+
+	PLU_DEV const ref_node* ref_nodes() const { return (const ref_node*)(blob + off_ref_nodes); }
+	PLU_DEV const float4* prim(int32_t s) const { return (const float4*)(blob + off_prim) + 3 * s; }
+	PLU_DEV int4 prim_meta(int32_t s) const { return ((const int4*)(blob + off_prim_meta))[s]; }   // tag, material, light, tie rank
+	PLU_DEV const plu_material_desc& material(int32_t m) const { return ((const plu_material_desc*)(blob + off_material))[m]; }
+	PLU_DEV const plu_texture_desc& texture(int32_t t) const { return ((const plu_texture_desc*)(blob + off_texture))[t]; }
+	PLU_DEV const plu_light_desc& light(int32_t l) const { return ((const plu_light_desc*)(blob + off_light))[l]; }
+};
+
+// Blobs up to this size are staged to shared memory by every CTA.
+#define PLU_SMEM_BLOB_MAX 16384
+
+// Stage the blob (call from all threads of the CTA; contains __syncthreads()).
+PLU_DEV void stage_scene(scene_ref& sc, unsigned char* smem) {
+	const uint4* src = (const uint4*)sc.blob;
+	uint4* dst = (uint4*)smem;
+	uint32_t n = sc.blob_bytes >> 4;
+	for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldg(src + i);
+	__syncthreads();
+	sc.blob = smem;
+}
+
+}  // namespace plud

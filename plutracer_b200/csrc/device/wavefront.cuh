@@ -1,0 +1,371 @@
+// wavefront.cuh — the wavefront kernels that replace the per-pixel recursive path loop
+// (reference src/renderer.cpp:59-150: render -> ray_color -> uniform_sample_one_light ->
+// estimate_direct_light).
+//
+//   k_generate    camera::generate_ray for every path slot of the wave            (camera.h:25-37)
+//   k_extend      scene->hit for the queued paths, compacts the hits              (renderer.cpp:61,86)
+//   k_shade       Le, material -> bsdf, light pick + light/BSDF sampling (the NEE
+//                 terms of estimate_direct_light up to the visibility test), BSDF
+//                 continuation sample, throughput update; emits shadow-ray
+//                 entries and the next extend queue                               (renderer.cpp:5-57,66-83)
+//   k_connect     shadow / MIS connection rays, adds the NEE term to the path     (renderer.cpp:16-24,41-47)
+//   k_accumulate  target->pixel(px) += L * (1/n^2) in sample order               (renderer.cpp:132)
+//
+// Paths live in slot-indexed structure-of-arrays buffers (128-bit rows); kernels are linked by
+// queues of slot ids compacted with a warp ballot + popc prefix and ONE atomicAdd per warp.
+// All kernels are persistent grid-stride loops whose trip count is read from a device counter, so a
+// whole wave is enqueued without any host synchronisation.
+#pragma once
+#include "shade.cuh"
+
+namespace plud {
+
+struct wave_buffers {
+	float4* ray_o;        // e.xyz, hit_record::t the next scene->hit starts from (only read by a leaf root)
+	float4* ray_d;        // d.xyz, flags
+	int2* hit;            // (t bits, surface id)
+	float4* thr[2];       // path_throughput, ping-pong by bounce parity
+	float4* rad;          // L
+	uint32_t* queue[2];   // extend queues, ping-pong
+	uint32_t* q_hit;      // paths whose extension ray hit
+	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
+	uint32_t* counters;   // [bounce*4 + {0: extend, 1: hit, 2: shadow}]
+	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries
+};
+
+#define FLAG_SPEC 1      // spec_bounce (renderer.cpp:79)
+#define FLAG_NONFINITE 2 // path_throughput holds an inf/NaN: `L += T * 0` terms are no longer no-ops
+
+#define SH_NEED1 1u
+#define SH_NEED2 2u
+#define SH_DELTA 4u
+
+struct wave_desc {
+	int32_t width, height;      // target->size
+	int32_t n_strata;           // sample_count.x
+	int32_t pix0, npix;         // pixel range of this wave (row-major; >= W*H: overflow-column strip, row = pix - W*H)
+	int32_t k0, kcount;         // ordinals of the samples of this wave
+	int32_t sample_begin, sample_stride;   // sample index s = begin + (k0 + k) * stride
+	int32_t max_vertices;
+	uint32_t seed_lo, seed_hi;
+	uint32_t n_slots;           // npix * kcount
+	int32_t use_lens;
+};
+
+PLU_DEV void slot_to_path(const wave_desc& w, uint32_t slot, philox_key& key, int32_t& px, int32_t& py, int32_t& s) {
+	uint32_t q = slot % (uint32_t)w.npix, k = slot / (uint32_t)w.npix;
+	int32_t pix = w.pix0 + (int32_t)q;
+	s = w.sample_begin + (w.k0 + (int32_t)k) * w.sample_stride;
+	int32_t wh = w.width * w.height;
+	if (pix >= wh) { px = w.width; py = pix - wh; } else { px = pix % w.width; py = pix / w.width; }
+	key.pixel = (uint32_t)pix; key.sample = (uint32_t)s; key.k0 = w.seed_lo; key.k1 = w.seed_hi;
+}
+
+// Warp-aggregated queue push: every lane of the warp must call it (converged).
+PLU_DEV uint32_t queue_push(uint32_t* counter, bool pred) {
+	unsigned mask = __ballot_sync(0xffffffffu, pred);
+	if (mask == 0) return 0;
+	unsigned lane = threadIdx.x & 31u;
+	int leader = __ffs(mask) - 1;
+	uint32_t base = 0;
+	if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+}
+
+extern __shared__ uint4 plu_smem[];
+
+// ---- k_generate -----------------------------------------------------------------------------------------------
+// stratified_sampler::generate_samples for one sample (sampler.h:58-69): stratum (s % n, s / n),
+// px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.
+__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb) {
+	for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < w.n_slots; slot += gridDim.x * blockDim.x) {
+		philox_key key; int32_t px_x, px_y, s;
+		slot_to_path(w, slot, key, px_x, px_y, s);
+		u4 o = philox_call(key, 0u);
+		int32_t n = w.n_strata;
+		float dp = 1.f / (float)(uint32_t)n;
+		float sx = (float)(s % n), sy = (float)(s / n);
+		f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);
+		f2 lens = mk2((sx + u01(o.z) * 0.999f) * dp, (sy + u01(o.w) * 0.999f) * dp);
+		ray r = generate_ray(sc_in.cam, px, lens, w.use_lens != 0);
+		wb.ray_o[slot] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
+		wb.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
+		wb.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
+}
+
+// ---- k_extend -------------------------------------------------------------------------------------------------
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce, uint32_t n_identity) {
+	scene_ref sc = sc_in;
+	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * 4 + 0];
+	const uint32_t* q = wb.queue[bounce & 1];
+	uint32_t* cnt_hit = wb.counters + bounce * 4 + 1;
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 0, (unsigned long long)n);
+	trace_counts tc; tc.nodes = 0; tc.prims = 0;
+	const uint32_t lane = threadIdx.x & 31u;
+	for (uint32_t j0 = blockIdx.x * blockDim.x + threadIdx.x - lane; j0 < n; j0 += gridDim.x * blockDim.x) {
+		uint32_t j = j0 + lane;
+		bool active = j < n, hit = false;
+		uint32_t slot = 0;
+		if (active) {
+			slot = bounce == 0 ? j : q[j];
+			float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
+			ray r; r.e = mk3(o); r.d = mk3(d);
+			float t; int32_t prim;
+			hit = trace_scene<COUNT>(sc, r, o.w, t, prim, &tc);
+			if (hit) wb.hit[slot] = make_int2(__float_as_int(t), prim);
+			else {
+				// renderer.cpp:87-90: after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
+				// a no-op unless T is not finite
+				int flags = __float_as_int(d.w);
+				if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
+					f3 T = mk3(wb.thr[bounce & 1][slot]); f3 L = mk3(wb.rad[slot]);
+					for (int32_t i = 0; i < sc.n_lights; ++i) L = L + T * mk3(0.f);
+					wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+				}
+			}
+		}
+		uint32_t at = queue_push(cnt_hit, hit);
+		if (hit) wb.q_hit[at] = slot;
+	}
+	if (COUNT) {
+		unsigned long long a = tc.nodes, b = tc.prims;
+		for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
+		if (lane == 0) { atomicAdd(wb.stats + 2, a); atomicAdd(wb.stats + 3, b); }
+	}
+}
+
+// ---- k_shade --------------------------------------------------------------------------------------------------
+// One path vertex: everything renderer.cpp:66-83 does between two scene->hit calls, except the
+// visibility tests of estimate_direct_light, which become shadow entries for k_connect.
+template <bool SMEM>
+__global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
+	scene_ref sc = sc_in;
+	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	const uint32_t n = wb.counters[bounce * 4 + 1];
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
+	uint32_t* cnt_shadow = wb.counters + bounce * 4 + 2;
+	uint32_t* cnt_next = wb.counters + (bounce + 1) * 4 + 0;
+	uint32_t* q_next = wb.queue[(bounce + 1) & 1];
+	const float4* thr_in = wb.thr[bounce & 1];
+	float4* thr_out = wb.thr[(bounce + 1) & 1];
+	const uint32_t lane = threadIdx.x & 31u;
+	const float nl = (float)sc.n_lights;
+	for (uint32_t j0 = blockIdx.x * blockDim.x + threadIdx.x - lane; j0 < n; j0 += gridDim.x * blockDim.x) {
+		uint32_t j = j0 + lane;
+		bool active = j < n, need_entry = false, go_on = false;
+		uint32_t slot = 0, sh_flags = 0;
+		f3 p = mk3(0.f), wi1 = mk3(0.f), c1 = mk3(0.f), wi2 = mk3(0.f), c2 = mk3(0.f);
+		if (active) {
+			slot = wb.q_hit[j];
+			float4 o4 = wb.ray_o[slot], d4 = wb.ray_d[slot];
+			int2 h = wb.hit[slot];
+			ray r; r.e = mk3(o4); r.d = mk3(d4);
+			int flags = __float_as_int(d4.w);
+			float t = __int_as_float(h.x); int32_t prim = h.y;
+			int4 meta = sc.prim_meta(prim);   // tag, material, light, -
+			const plu_material_desc& m = sc.material(meta.y);
+			hit_rec hr; fill_record(sc, prim, meta.x, r, t, m.texture >= 0, hr);
+			f3 T = bounce == 0 ? mk3(1.f) : mk3(thr_in[slot]);
+			philox_key key; int32_t px_x, px_y, s;
+			slot_to_path(w, slot, key, px_x, px_y, s);
+			vertex_rng rng; rng.begin(key, bounce);
+			p = ray_at(r, t);
+			f3 nrm = hr.norm, wo = -r.d;
+			// renderer.cpp:66: emitted light at the first vertex or after a specular bounce
+			if ((bounce == 0 || (flags & FLAG_SPEC)) && (meta.z >= 0 || (flags & FLAG_NONFINITE))) {
+				f3 Le = meta.z >= 0 ? area_L(sc.light(meta.z), nrm, -r.d) : mk3(0.f);
+				f3 L = mk3(wb.rad[slot]);
+				L = L + T * Le;
+				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+			}
+			bsdf b; make_bsdf(sc, m, hr, b);
+			// renderer.cpp:53-57 + :5-51 up to the visibility tests
+			if (sc.n_lights > 0) {
+				int32_t li = (int32_t)gmin(floorf(rng.light_pick() * nl), nl - 1.f);
+				const plu_light_desc& l = sc.light(li);
+				bool is_delta = l.tag == PLU_LIGHT_POINT;
+				int32_t ltag = is_delta ? 0 : sc.prim_meta(l.prim).x;
+				f3 Li, wi; float light_pdf;
+				if (is_delta) {   // point_light::sampleL, light.h:20-27
+					f3 l2p = mk3(l.a[0], l.a[1], l.a[2]) - p;
+					float len2 = dot(l2p, l2p);
+					wi = l2p / sqrtf(len2);
+					light_pdf = 1.f;
+					Li = mk3(l.b[0], l.b[1], l.b[2]) / len2;
+				} else {   // diffuse_area_light::sampleL, area_light.h:25-31
+					f3 ln, ps = surface_sample(sc, l.prim, ltag, rng.light_u(), ln, rng);
+					wi = normalize(ps - p);
+					light_pdf = surface_pdf(sc, l.prim, ltag, l.area, p, wi);
+					Li = area_L(l, ln, -wi);
+				}
+				if (light_pdf > 0.f && dot(Li, Li) > 0.f) {
+					f3 f = b.F(nrm, wo, wi, BX_NEE_TYPES);
+					if (dot(f, f) > 0.f) {
+						sh_flags |= SH_NEED1; wi1 = wi;
+						if (is_delta) c1 = f * Li * (fabsf(dot(wi, nrm)) / light_pdf);
+						else {
+							float bsdf_pdf = b.pdf(wo, wi, BX_NEE_TYPES);
+							float wgt = (bsdf_pdf * bsdf_pdf) / (bsdf_pdf * bsdf_pdf + light_pdf * light_pdf);
+							c1 = f * Li * (fabsf(dot(wi, nrm)) * wgt / light_pdf);
+						}
+					}
+				}
+				if (!is_delta) {   // BSDF-sampled MIS term, renderer.cpp:29-49
+					uint32_t sampled = 0; float bsdf_pdf;
+					f3 f = b.sampleF(rng, 0, nrm, wo, wi, bsdf_pdf, BX_NEE_TYPES, sampled);
+					if (dot(f, f) > 0.f && bsdf_pdf > 0.f) {
+						float wgt = 1.f; bool live = true;
+						if (!(sampled & BX_SPECULAR)) {
+							float lp = surface_pdf(sc, l.prim, ltag, l.area, p, wi);
+							if (lp == 0.f) live = false;
+							else wgt = (bsdf_pdf * bsdf_pdf) / (bsdf_pdf * bsdf_pdf + lp * lp);
+						}
+						if (live) {
+							// Li = lihr.surf->mat->Le(p, n, -wi) uses the SHADING point's normal (renderer.cpp:43), so it
+							// is known before the ray is cast; a zero Li makes the cast unobservable and it is skipped
+							f3 Li2 = area_L(l, nrm, -wi);
+							if (dot(Li2, Li2) > 0.f) {
+								sh_flags |= SH_NEED2; wi2 = wi;
+								c2 = f * Li2 * fabsf(dot(wi, nrm)) * wgt / bsdf_pdf;
+							}
+						}
+					}
+				}
+				if (is_delta) sh_flags |= SH_DELTA;
+				sh_flags |= (uint32_t)li << 8;
+				need_entry = (sh_flags & (SH_NEED1 | SH_NEED2)) != 0;
+			}
+			if (!need_entry && (flags & FLAG_NONFINITE)) {   // L += T * (nl * 0): only observable when T is not finite
+				f3 L = mk3(wb.rad[slot]);
+				L = L + T * (nl * mk3(0.f));
+				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+			}
+			// renderer.cpp:76-83: continuation
+			if (bounce < w.max_vertices - 1) {
+				uint32_t types = 0; float pdf; f3 wi;
+				f3 f = b.sampleF(rng, 1, nrm, wo, wi, pdf, BX_ALL, types);
+				if (!(dot(f, f) == 0.f || pdf == 0.f)) {
+					T = T * (f * fabsf(dot(wi, nrm)) / pdf);
+					int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
+					wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
+					wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
+					thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
+					go_on = true;
+				}
+			}
+		}
+		uint32_t at = queue_push(cnt_shadow, need_entry);
+		if (need_entry) {
+			wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
+			wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
+			wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
+			if (sh_flags & SH_NEED2) {
+				wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
+				wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
+			}
+		}
+		uint32_t an = queue_push(cnt_next, go_on);
+		if (go_on) q_next[an] = slot;
+	}
+}
+
+// ---- k_connect ------------------------------------------------------------------------------------------------
+// The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
+// `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(256) k_connect(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce) {
+	scene_ref sc = sc_in;
+	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	const uint32_t n = wb.counters[bounce * 4 + 2];
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
+	const float4* thr_in = wb.thr[bounce & 1];
+	const float nl = (float)sc.n_lights;
+	trace_counts tc; tc.nodes = 0; tc.prims = 0;
+	uint32_t rays = 0;
+	const uint32_t lane = threadIdx.x & 31u;
+	for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+		float4 p4 = wb.sh_p[j], w1 = wb.sh_w1[j];
+		uint32_t slot = __float_as_uint(p4.w), fl = __float_as_uint(w1.w);
+		int32_t li = (int32_t)(fl >> 8);
+		f3 Ld = mk3(0.f);
+		bool any = false;
+		ray r; r.e = mk3(p4);
+		if (fl & SH_NEED1) {
+			r.d = mk3(w1);
+			float t; int32_t prim;
+			rays++;
+			bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+			// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
+			if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(wb.sh_c1[j]); any = true; }
+		}
+		if (fl & SH_NEED2) {
+			r.d = mk3(wb.sh_w2[j]);
+			float t; int32_t prim;
+			rays++;
+			bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+			if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(wb.sh_c2[j]); any = true; }
+		}
+		f3 T = bounce == 0 ? mk3(1.f) : mk3(thr_in[slot]);
+		if (any || !finite3(T)) {
+			f3 L = mk3(wb.rad[slot]);
+			L = L + T * (nl * Ld);
+			wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+		}
+	}
+	unsigned long long a = rays, b = tc.nodes, c = tc.prims;
+	for (int o = 16; o > 0; o >>= 1) {
+		a += __shfl_down_sync(0xffffffffu, a, o);
+		if (COUNT) { b += __shfl_down_sync(0xffffffffu, b, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+	}
+	if (lane == 0) {
+		if (a) atomicAdd(wb.stats + 1, a);
+		if (COUNT) { atomicAdd(wb.stats + 2, b); atomicAdd(wb.stats + 3, c); }
+	}
+}
+
+// ---- k_accumulate ---------------------------------------------------------------------------------------------
+// target->pixel(floor(px)) += ray_color * smp_wgt, samples in ascending order (renderer.cpp:132).
+// The overflow-column strip (pixel index >= W*H, sampler.h:74-78) lands in pixel (0, row+1).
+__global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave_desc w, wave_buffers wb, float* fb, float smp_wgt) {
+	for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < (uint32_t)w.npix; q += gridDim.x * blockDim.x) {
+		int32_t pix = w.pix0 + (int32_t)q, wh = w.width * w.height;
+		int32_t dst = pix < wh ? pix : (pix - wh + 1) * w.width;
+		if (dst >= wh) continue;   // the reference writes one vec3 past the buffer here
+		float* o = fb + (size_t)dst * 3;
+		f3 acc = mk3(o[0], o[1], o[2]);
+		for (int32_t k = 0; k < w.kcount; ++k) {
+			f3 c = mk3(wb.rad[(size_t)k * (size_t)w.npix + q]);
+			acc = acc + c * smp_wgt;
+		}
+		o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;
+	}
+}
+
+// ---- parity hooks ---------------------------------------------------------------------------------------------
+// scene->hit for explicit rays: surface id, t, hit_record::norm.
+template <bool SMEM>
+__global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ scene_ref sc_in, int64_t n, const float* o3, const float* d3,
+                                                    int primary_w, int primary_h, int32_t* id, float* t_out, float* n3) {
+	scene_ref sc = sc_in;
+	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+		ray r;
+		if (primary_w > 0) {   // pixel-centre pinhole rays
+			int32_t x = (int32_t)(i % primary_w), y = (int32_t)(i / primary_w);
+			r = generate_ray(sc.cam, mk2((float)x + .5f, (float)y + .5f), mk2(.5f, .5f), false);
+		} else {
+			r.e = mk3(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2]); r.d = mk3(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2]);
+		}
+		float t; int32_t prim; trace_counts tc;
+		if (trace_scene<false>(sc, r, PLU_T_MAX, t, prim, &tc)) {
+			hit_rec hr; fill_record(sc, prim, sc.prim_meta(prim).x, r, t, false, hr);
+			id[i] = prim; t_out[i] = t; n3[3 * i] = hr.norm.x; n3[3 * i + 1] = hr.norm.y; n3[3 * i + 2] = hr.norm.z;
+		} else { id[i] = -1; t_out[i] = 0.f; n3[3 * i] = 0.f; n3[3 * i + 1] = 0.f; n3[3 * i + 2] = 0.f; }
+	}
+}
+
+}  // namespace plud

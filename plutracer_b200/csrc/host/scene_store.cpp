@@ -186,6 +186,19 @@ extern "C" void plu_scene_get_defaults(const plu_scene* s, int32_t* width, int32
 	if (n_strata) *n_strata = s->n_strata;
 }
 
+extern "C" int plu_scene_override(plu_scene* s, int32_t width, int32_t height, int32_t n_strata) {
+	if (!s) return PLU_E_ARG;
+	if (width > 0 && height > 0) {
+		s->width = width; s->height = height;
+		// camera ctor: inv_image_size(1.f / (vec2)target_size), camera.h:18
+		s->cam.inv_image_size[0] = 1.f / (float)(uint32_t)width;
+		s->cam.inv_image_size[1] = 1.f / (float)(uint32_t)height;
+	}
+	if (n_strata > 0) s->n_strata = n_strata;
+	s->seal();
+	return PLU_OK;
+}
+
 extern "C" void plu_scene_free(plu_scene* s) { delete s; }
 
 extern "C" uint32_t plu_abi_version(void) { return PLUGPU_ABI_VERSION; }

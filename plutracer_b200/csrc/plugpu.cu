@@ -1,0 +1,480 @@
+// plugpu.cu — C ABI of libplugpu.so (include/plugpu.h): context, scene upload, wave scheduling.
+// Replaces plu::renderer::render (reference src/renderer.cpp:98-150) and its callees behind the
+// drop-in boundary of SURVEY.md 8b.  There is no CPU fallback: every entry point that needs the GPU
+// fails with PLU_E_CUDA when no device is usable.
+#include "device/wavefront.cuh"
+#include "host/bvh_build.h"
+#include "host/scene_store.h"
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace plud;
+
+static_assert(sizeof(pluhost::ref_node_h) == sizeof(ref_node), "ref node layout");
+static_assert(sizeof(pluhost::fast_node_h) == sizeof(fast_node), "fast node layout");
+
+static thread_local std::string g_create_error;
+
+struct plu_gpu_ctx {
+	int device = 0;
+	int sm_count = 0;
+	cudaStream_t stream = nullptr;
+	std::string err;
+	// scene
+	bool have_scene = false;
+	scene_ref sc{};
+	unsigned char* d_blob = nullptr;
+	float *d_tri_uv = nullptr, *d_tri_normal = nullptr, *d_texels = nullptr;
+	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr;
+	bool blob_in_smem = false;
+	bool use_fast = false;
+	int32_t fast_threshold = 64;   // scenes with more surfaces than this use the fast BVH by default
+	// wave buffers
+	uint32_t capacity = 0;         // path slots
+	wave_buffers wb{};
+	void* d_wave_mem = nullptr;
+	float* d_fb = nullptr; size_t fb_floats = 0;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	int grid_generate = 0, grid_extend = 0, grid_shade = 0, grid_connect = 0;
+};
+
+#define CU(call)                                                                                         \
+	do {                                                                                                 \
+		cudaError_t e_ = (call);                                                                         \
+		if (e_ != cudaSuccess) {                                                                         \
+			ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                               \
+			return PLU_E_CUDA;                                                                           \
+		}                                                                                                \
+	} while (0)
+
+static int fail(plu_gpu_ctx* ctx, int code, const std::string& msg) { ctx->err = msg; return code; }
+
+extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
+	if (!out) return PLU_E_ARG;
+	*out = nullptr;
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count <= 0) {
+		g_create_error = std::string("no usable CUDA device (libplugpu has no CPU fallback): ") + cudaGetErrorString(e);
+		return PLU_E_CUDA;
+	}
+	if (device < 0 || device >= count) { g_create_error = "device index out of range"; return PLU_E_ARG; }
+	plu_gpu_ctx* ctx = new plu_gpu_ctx;
+	ctx->device = device;
+	cudaDeviceProp prop;
+	if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+		g_create_error = std::string("CUDA context set-up failed: ") + cudaGetErrorString(e);
+		delete ctx;
+		return PLU_E_CUDA;
+	}
+	ctx->sm_count = prop.multiProcessorCount;
+	*out = ctx;
+	return PLU_OK;
+}
+
+static void free_scene(plu_gpu_ctx* ctx) {
+	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
+	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index);
+	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
+	ctx->have_scene = false;
+}
+
+extern "C" void plu_gpu_destroy(plu_gpu_ctx* ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	free_scene(ctx);
+	cudaFree(ctx->d_wave_mem); cudaFree(ctx->d_fb);
+	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+extern "C" const char* plu_gpu_last_error(const plu_gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+// ---- scene upload ---------------------------------------------------------------------------------------------
+template <class T>
+static uint32_t blob_put(std::vector<unsigned char>& blob, const T* p, size_t n) {
+	size_t off = (blob.size() + 15) & ~(size_t)15;
+	blob.resize(off + std::max<size_t>(n * sizeof(T), 16));
+	if (n) std::memcpy(blob.data() + off, p, n * sizeof(T));
+	return (uint32_t)off;
+}
+
+extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
+	if (!ctx) return PLU_E_ARG;
+	std::string v = pluhost::validate_desc(d);
+	if (!v.empty()) return fail(ctx, PLU_E_ARG, v);
+	CU(cudaSetDevice(ctx->device));
+	free_scene(ctx);
+	size_t n = (size_t)d->n_prims;
+
+	std::vector<int32_t> rank;
+	if (d->prim_tie_rank) rank.assign(d->prim_tie_rank, d->prim_tie_rank + n);
+	else pluhost::reference_leaf_order(d, rank);
+	{   // the tie ranks must be a permutation
+		std::vector<char> seen(n, 0);
+		for (size_t i = 0; i < n; ++i) { if (rank[i] < 0 || (size_t)rank[i] >= n || seen[(size_t)rank[i]]) return fail(ctx, PLU_E_ARG, "prim_tie_rank is not a permutation"); seen[(size_t)rank[i]] = 1; }
+	}
+	std::vector<pluhost::ref_node_h> ref_nodes;
+	bool use_fast = d->n_prims > ctx->fast_threshold;
+	// the reference tree of a huge scene is only needed in verification mode; it is still built (O(n))
+	pluhost::build_ref_nodes(d, rank, ref_nodes);
+
+	std::vector<int32_t> meta(4 * n);
+	for (size_t s = 0; s < n; ++s) {
+		const plu_material_desc& m = d->materials[d->prim_material[s]];
+		meta[4 * s] = d->prim_tag[s]; meta[4 * s + 1] = d->prim_material[s];
+		meta[4 * s + 2] = m.tag == PLU_MAT_EMISSION ? m.light : -1;   // material::area_light()
+		meta[4 * s + 3] = rank[s];
+	}
+	std::vector<unsigned char> blob;
+	scene_ref sc{};
+	sc.off_ref_nodes = blob_put(blob, ref_nodes.data(), ref_nodes.size());
+	sc.off_prim = blob_put(blob, d->prim_data, n * 12);
+	sc.off_prim_meta = blob_put(blob, meta.data(), meta.size());
+	sc.off_material = blob_put(blob, d->materials, (size_t)d->n_materials);
+	sc.off_texture = blob_put(blob, d->textures, (size_t)d->n_textures);
+	sc.off_light = blob_put(blob, d->lights, (size_t)d->n_lights);
+	blob.resize((blob.size() + 15) & ~(size_t)15);
+	sc.blob_bytes = (uint32_t)blob.size();
+	sc.n_ref_nodes = (int32_t)ref_nodes.size();
+	sc.n_prims = d->n_prims; sc.n_materials = d->n_materials; sc.n_textures = d->n_textures; sc.n_lights = d->n_lights;
+	sc.cam = d->cam;
+	CU(cudaMalloc(&ctx->d_blob, blob.size()));
+	CU(cudaMemcpy(ctx->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+	sc.blob = ctx->d_blob;
+	if (d->prim_tri_uv && d->prim_tri_normal && n) {
+		CU(cudaMalloc(&ctx->d_tri_uv, n * 6 * sizeof(float))); CU(cudaMemcpy(ctx->d_tri_uv, d->prim_tri_uv, n * 6 * sizeof(float), cudaMemcpyHostToDevice));
+		CU(cudaMalloc(&ctx->d_tri_normal, n * 9 * sizeof(float))); CU(cudaMemcpy(ctx->d_tri_normal, d->prim_tri_normal, n * 9 * sizeof(float), cudaMemcpyHostToDevice));
+	}
+	if (d->image_texels && d->n_image_texels > 0) {
+		size_t bytes = (size_t)d->n_image_texels * 3 * sizeof(float);
+		CU(cudaMalloc(&ctx->d_texels, bytes)); CU(cudaMemcpy(ctx->d_texels, d->image_texels, bytes, cudaMemcpyHostToDevice));
+	}
+	sc.tri_uv = ctx->d_tri_uv; sc.tri_normal = ctx->d_tri_normal; sc.texels = ctx->d_texels;
+	{
+		std::vector<pluhost::fast_node_h> fn; std::vector<int32_t> fi;
+		pluhost::build_fast_bvh(d, fn, fi);
+		if (!fn.empty()) {
+			CU(cudaMalloc(&ctx->d_fast, fn.size() * sizeof(fast_node))); CU(cudaMemcpy(ctx->d_fast, fn.data(), fn.size() * sizeof(fast_node), cudaMemcpyHostToDevice));
+			CU(cudaMalloc(&ctx->d_fast_index, fi.size() * sizeof(int32_t))); CU(cudaMemcpy(ctx->d_fast_index, fi.data(), fi.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+		}
+		sc.n_fast_nodes = (int32_t)fn.size();
+	}
+	sc.fast_nodes = use_fast ? ctx->d_fast : nullptr;
+	ctx->use_fast = use_fast;
+	sc.fast_prim_index = ctx->d_fast_index;
+	ctx->sc = sc;
+	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
+	ctx->have_scene = true;
+	return PLU_OK;
+}
+
+static void select_bvh(const plu_gpu_ctx* ctx, scene_ref& sc, uint32_t flags) {
+	if (flags & PLU_RENDER_BVH_REFERENCE) sc.fast_nodes = nullptr;
+	else if (flags & PLU_RENDER_BVH_FAST) sc.fast_nodes = ctx->d_fast;
+}
+
+// ---- wave buffers ---------------------------------------------------------------------------------------------
+#define PLU_MAX_VERTICES_CAP 64
+
+static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
+	if (ctx->capacity >= slots && ctx->d_wave_mem) return PLU_OK;
+	CU(cudaFree(ctx->d_wave_mem)); ctx->d_wave_mem = nullptr; ctx->capacity = 0;
+	size_t N = slots;
+	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+	size_t bytes = 10 * al(N * 16) + al(N * 8) + 3 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
+	CU(cudaMalloc(&ctx->d_wave_mem, bytes));
+	unsigned char* p = (unsigned char*)ctx->d_wave_mem;
+	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
+	wave_buffers& wb = ctx->wb;
+	// 16-byte rows first so every array is 256-byte aligned
+	wb.ray_o = (float4*)take(N * 16); wb.ray_d = (float4*)take(N * 16);
+	wb.thr[0] = (float4*)take(N * 16); wb.thr[1] = (float4*)take(N * 16); wb.rad = (float4*)take(N * 16);
+	wb.sh_p = (float4*)take(N * 16); wb.sh_w1 = (float4*)take(N * 16); wb.sh_c1 = (float4*)take(N * 16);
+	wb.sh_w2 = (float4*)take(N * 16); wb.sh_c2 = (float4*)take(N * 16);
+	wb.hit = (int2*)take(N * 8);
+	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4); wb.q_hit = (uint32_t*)take(N * 4);
+	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t));
+	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
+	if ((size_t)(p - (unsigned char*)ctx->d_wave_mem) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
+	ctx->capacity = slots;
+	return PLU_OK;
+}
+
+template <class K>
+static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
+	int occ = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+	return ctx->sm_count * occ;
+}
+
+struct launch_cfg { bool smem, count; size_t smem_bytes; int g_gen, g_ext, g_shade, g_conn, g_acc; };
+
+static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
+	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.smem_bytes = c.smem ? ctx->sc.blob_bytes : 0;
+	c.g_gen = grid_for(ctx, k_generate, 0);
+	c.g_acc = grid_for(ctx, k_accumulate, 0);
+#define PICK(var, K) \
+	var = c.smem ? (count ? grid_for(ctx, K<true, true>, c.smem_bytes) : grid_for(ctx, K<true, false>, c.smem_bytes)) \
+	             : (count ? grid_for(ctx, K<false, true>, 0) : grid_for(ctx, K<false, false>, 0))
+	PICK(c.g_ext, k_extend); PICK(c.g_conn, k_connect);
+#undef PICK
+	c.g_shade = c.smem ? grid_for(ctx, k_shade<true>, c.smem_bytes) : grid_for(ctx, k_shade<false>, 0);
+	return c;
+}
+
+// PLU_RENDER_PROFILE: one event after every launch of a wave; the gaps are summed per kernel class.
+struct wave_profiler {
+	bool on = false;
+	std::vector<cudaEvent_t> ev;
+	std::vector<int> cls;       // class of the launch that ENDS at event i (0 gen, 1 extend, 2 shade, 3 connect, 4 accumulate, -1 start)
+	double ms[5] = {0, 0, 0, 0, 0};
+	size_t used = 0;
+	void mark(int c, cudaStream_t st) {
+		if (!on) return;
+		if (used == ev.size()) { cudaEvent_t e; cudaEventCreate(&e); ev.push_back(e); cls.push_back(0); }
+		cls[used] = c; cudaEventRecord(ev[used], st); used++;
+	}
+	void collect(cudaStream_t st) {
+		if (!on || used == 0) return;
+		cudaStreamSynchronize(st);
+		for (size_t i = 1; i < used; ++i) if (cls[i] >= 0) { float m = 0.f; cudaEventElapsedTime(&m, ev[i - 1], ev[i]); ms[cls[i]] += m; }
+		used = 0;
+	}
+	~wave_profiler() { for (auto e : ev) cudaEventDestroy(e); }
+};
+
+// Enqueue one wave (generate -> [extend, shade, connect] x max_vertices); returns the launch count.
+static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& w, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr) {
+	wave_buffers& wb = ctx->wb;
+	wave_profiler none; if (!pf) pf = &none;
+	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * 4 * sizeof(uint32_t), st);
+	pf->mark(-1, st);
+	k_generate<<<c.g_gen, 256, 0, st>>>(sc, w, wb);
+	pf->mark(0, st);
+	int launches = 1;
+	for (int b = 0; b < w.max_vertices; ++b) {
+		if (c.smem) {
+			if (c.count) k_extend<true, true><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
+			else k_extend<true, false><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
+			pf->mark(1, st);
+			k_shade<true><<<c.g_shade, 256, c.smem_bytes, st>>>(sc, w, wb, b);
+			pf->mark(2, st);
+			if (c.count) k_connect<true, true><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
+			else k_connect<true, false><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
+			pf->mark(3, st);
+		} else {
+			if (c.count) k_extend<false, true><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
+			else k_extend<false, false><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
+			pf->mark(1, st);
+			k_shade<false><<<c.g_shade, 256, 0, st>>>(sc, w, wb, b);
+			pf->mark(2, st);
+			if (c.count) k_connect<false, true><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
+			else k_connect<false, false><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
+			pf->mark(3, st);
+		}
+		launches += 3;
+	}
+	return launches;
+}
+
+static int check_params(plu_gpu_ctx* ctx, const plu_render_params* p) {
+	if (!p) return fail(ctx, PLU_E_ARG, "render params are NULL");
+	if (p->width <= 0 || p->height <= 0 || p->n_strata <= 0) return fail(ctx, PLU_E_ARG, "width, height and n_strata must be positive");
+	if ((int64_t)p->width * p->height > (int64_t)1 << 30) return fail(ctx, PLU_E_ARG, "image too large");
+	if (p->n_strata > 32768) return fail(ctx, PLU_E_ARG, "n_strata too large");
+	if (p->max_vertices < 0 || p->max_vertices > PLU_MAX_VERTICES_CAP) return fail(ctx, PLU_E_ARG, "max_vertices out of range");
+	if (p->sample_count < 0 || (p->sample_count > 0 && (p->sample_stride <= 0 || p->sample_begin < 0))) return fail(ctx, PLU_E_ARG, "bad sample range");
+	if (!ctx->have_scene) return fail(ctx, PLU_E_NOSCENE, "no scene uploaded");
+	return PLU_OK;
+}
+
+static wave_desc base_desc(const plu_scene_desc*, const plu_render_params* p, const scene_ref& sc) {
+	wave_desc w{};
+	w.width = p->width; w.height = p->height; w.n_strata = p->n_strata;
+	w.sample_begin = p->sample_count > 0 ? p->sample_begin : 0;
+	w.sample_stride = p->sample_count > 0 ? p->sample_stride : 1;
+	w.max_vertices = p->max_vertices > 0 ? p->max_vertices : 8;
+	w.seed_lo = (uint32_t)p->seed; w.seed_hi = (uint32_t)(p->seed >> 32);
+	w.use_lens = sc.cam.lens_radius > 0.f ? 1 : 0;
+	return w;
+}
+
+extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb, void* stream, plu_render_stats* stats) {
+	if (!ctx) return PLU_E_ARG;
+	int rc = check_params(ctx, p);
+	if (rc != PLU_OK) return rc;
+	if (!d_rgb) return fail(ctx, PLU_E_ARG, "framebuffer pointer is NULL");
+	CU(cudaSetDevice(ctx->device));
+	cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+	scene_ref sc = ctx->sc;
+	select_bvh(ctx, sc, p->flags);
+	wave_desc w = base_desc(nullptr, p, sc);
+	const int64_t wh = (int64_t)p->width * p->height;
+	const int32_t spp = p->n_strata * p->n_strata;
+	const int32_t count = p->sample_count > 0 ? p->sample_count : spp;
+	const float smp_wgt = 1.f / (float)(uint32_t)spp;   // renderer.cpp:100
+	uint32_t want = p->strata_per_wave > 0 ? (uint32_t)std::min<int64_t>(wh * p->strata_per_wave, (int64_t)1 << 26) : (1u << 22);
+	want = (uint32_t)std::min<int64_t>(want, wh * (int64_t)count);
+	want = std::max<uint32_t>(want, (uint32_t)std::min<int64_t>(wh, 1 << 22));
+	rc = ensure_wave(ctx, want);
+	if (rc != PLU_OK) return rc;
+	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
+	CU(cudaMemsetAsync(ctx->wb.stats, 0, 8 * sizeof(unsigned long long), st));
+	CU(cudaEventRecord(ctx->ev0, st));
+	uint64_t launches = 0, samples = 0;
+	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
+	// main image, then (compat) the overflow-column strip: sampler.h:74-78 renders x == W for rows 0..H-1
+	for (int pass = 0; pass < ((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? 2 : 1); ++pass) {
+		int64_t pbeg = pass == 0 ? 0 : wh, pend = pass == 0 ? wh : wh + p->height - 1;
+		for (int64_t p0 = pbeg; p0 < pend;) {
+			int64_t np = std::min<int64_t>(pend - p0, ctx->capacity);
+			int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->capacity / np));
+			for (int32_t k0 = 0; k0 < count; k0 += K) {
+				w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
+				w.n_slots = (uint32_t)(np * w.kcount);
+				launches += (uint64_t)enqueue_wave(ctx, sc, w, cfg, st, &prof);
+				k_accumulate<<<cfg.g_acc, 256, 0, st>>>(w, ctx->wb, d_rgb, smp_wgt);
+				prof.mark(4, st); prof.collect(st);
+				launches++;
+				samples += w.n_slots;
+			}
+			p0 += np;
+		}
+	}
+	CU(cudaEventRecord(ctx->ev1, st));
+	CU(cudaGetLastError());
+	CU(cudaStreamSynchronize(st));
+	if (stats) {
+		std::memset(stats, 0, sizeof(*stats));
+		unsigned long long h[8];
+		CU(cudaMemcpy(h, ctx->wb.stats, sizeof(h), cudaMemcpyDeviceToHost));
+		float ms = 0.f; CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+		stats->samples = samples; stats->rays_extend = h[0]; stats->rays_shadow = h[1];
+		stats->bvh_nodes_visited = h[2]; stats->prims_tested = h[3];
+		stats->ms_device = ms; stats->kernel_launches = launches;
+		stats->shade_vertices = h[4]; stats->shadow_entries = h[5];
+		stats->ms_generate = prof.ms[0]; stats->ms_extend = prof.ms[1]; stats->ms_shade = prof.ms[2];
+		stats->ms_connect = prof.ms[3]; stats->ms_accumulate = prof.ms[4];
+	}
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, float* out_rgb, plu_render_stats* stats) {
+	if (!ctx) return PLU_E_ARG;
+	int rc = check_params(ctx, p);
+	if (rc != PLU_OK) return rc;
+	if (!out_rgb) return fail(ctx, PLU_E_ARG, "out_rgb is NULL");
+	CU(cudaSetDevice(ctx->device));
+	size_t floats = (size_t)p->width * p->height * 3;
+	if (ctx->fb_floats < floats) {
+		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
+		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
+	}
+	// `+=` semantics (renderer.cpp:132): the device buffer starts from the caller's pixels
+	CU(cudaMemcpyAsync(ctx->d_fb, out_rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	rc = plu_gpu_render_device(ctx, p, ctx->d_fb, ctx->stream, stats);
+	if (rc != PLU_OK) return rc;
+	CU(cudaMemcpyAsync(out_rgb, ctx->d_fb, floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return PLU_OK;
+}
+
+// ---- parity hooks ---------------------------------------------------------------------------------------------
+static int trace_common(plu_gpu_ctx* ctx, int64_t n, const float* o3, const float* d3, int pw, int ph, uint32_t flags,
+                        int32_t* surf_id, float* t, float* normal3) {
+	if (!ctx->have_scene) return fail(ctx, PLU_E_NOSCENE, "no scene uploaded");
+	if (n < 0 || !surf_id || !t || !normal3) return fail(ctx, PLU_E_ARG, "bad trace arguments");
+	if (n == 0) return PLU_OK;
+	CU(cudaSetDevice(ctx->device));
+	scene_ref sc = ctx->sc;
+	select_bvh(ctx, sc, flags);
+	float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr, *d_n = nullptr; int32_t* d_id = nullptr;
+	int rc = PLU_OK;
+	auto cleanup = [&]() { cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_n); cudaFree(d_id); };
+#define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); cleanup(); return PLU_E_CUDA; } } while (0)
+	if (pw <= 0) {
+		CUX(cudaMalloc(&d_o, (size_t)n * 12)); CUX(cudaMalloc(&d_d, (size_t)n * 12));
+		CUX(cudaMemcpyAsync(d_o, o3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+		CUX(cudaMemcpyAsync(d_d, d3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	CUX(cudaMalloc(&d_id, (size_t)n * 4)); CUX(cudaMalloc(&d_t, (size_t)n * 4)); CUX(cudaMalloc(&d_n, (size_t)n * 12));
+	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+	if (ctx->blob_in_smem) k_trace_rays<true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+	else k_trace_rays<false><<<grid, 256, 0, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+	CUX(cudaGetLastError());
+	CUX(cudaMemcpyAsync(surf_id, d_id, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CUX(cudaMemcpyAsync(t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CUX(cudaMemcpyAsync(normal3, d_n, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	CUX(cudaStreamSynchronize(ctx->stream));
+#undef CUX
+	cleanup();
+	return rc;
+}
+
+extern "C" int plu_gpu_trace_primary(plu_gpu_ctx* ctx, int32_t width, int32_t height, uint32_t flags, int32_t* surf_id, float* t, float* normal3) {
+	if (!ctx) return PLU_E_ARG;
+	if (width <= 0 || height <= 0) return fail(ctx, PLU_E_ARG, "width and height must be positive");
+	return trace_common(ctx, (int64_t)width * height, nullptr, nullptr, width, height, flags, surf_id, t, normal3);
+}
+
+extern "C" int plu_gpu_trace_rays(plu_gpu_ctx* ctx, int64_t n, const float* origin3, const float* dir3, uint32_t flags, int32_t* surf_id, float* t, float* normal3) {
+	if (!ctx) return PLU_E_ARG;
+	if (n > 0 && (!origin3 || !dir3)) return fail(ctx, PLU_E_ARG, "ray arrays are NULL");
+	return trace_common(ctx, n, origin3, dir3, 0, 0, flags, surf_id, t, normal3);
+}
+
+extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params* p, int64_t pixel_begin, int64_t pixel_count, float* out_rgb) {
+	if (!ctx) return PLU_E_ARG;
+	int rc = check_params(ctx, p);
+	if (rc != PLU_OK) return rc;
+	const int64_t wh = (int64_t)p->width * p->height;
+	if (!out_rgb || pixel_begin < 0 || pixel_count < 0 || pixel_begin + pixel_count > wh + p->height) return fail(ctx, PLU_E_ARG, "bad pixel range");
+	if (pixel_count == 0) return PLU_OK;
+	CU(cudaSetDevice(ctx->device));
+	scene_ref sc = ctx->sc;
+	select_bvh(ctx, sc, p->flags);
+	wave_desc w = base_desc(nullptr, p, sc);
+	const int32_t count = p->sample_count > 0 ? p->sample_count : p->n_strata * p->n_strata;
+	rc = ensure_wave(ctx, (uint32_t)std::min<int64_t>((int64_t)1 << 22, std::max<int64_t>(pixel_count, 1) * count));
+	if (rc != PLU_OK) return rc;
+	launch_cfg cfg = make_cfg(ctx, false);
+	std::vector<float4> host;
+	for (int64_t p0 = pixel_begin; p0 < pixel_begin + pixel_count;) {
+		int64_t np = std::min<int64_t>(pixel_begin + pixel_count - p0, ctx->capacity);
+		int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->capacity / np));
+		for (int32_t k0 = 0; k0 < count; k0 += K) {
+			w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
+			w.n_slots = (uint32_t)(np * w.kcount);
+			enqueue_wave(ctx, sc, w, cfg, ctx->stream);
+			CU(cudaGetLastError());
+			host.resize(w.n_slots);
+			CU(cudaMemcpyAsync(host.data(), ctx->wb.rad, (size_t)w.n_slots * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaStreamSynchronize(ctx->stream));
+			for (int32_t k = 0; k < w.kcount; ++k)
+				for (int64_t q = 0; q < np; ++q) {
+					const float4& c = host[(size_t)k * (size_t)np + (size_t)q];
+					float* o = out_rgb + ((size_t)(p0 - pixel_begin + q) * (size_t)count + (size_t)(k0 + k)) * 3;
+					o[0] = c.x; o[1] = c.y; o[2] = c.z;
+				}
+		}
+		p0 += np;
+	}
+	return PLU_OK;
+}
+
+// ---- host-side helpers ------------------------------------------------------------------------------------------
+extern "C" int plu_scene_reference_leaf_order(const plu_scene_desc* desc, int32_t* rank) {
+	if (!rank || !pluhost::validate_desc(desc).empty()) return PLU_E_ARG;
+	std::vector<int32_t> r;
+	pluhost::reference_leaf_order(desc, r);
+	std::copy(r.begin(), r.end(), rank);
+	return PLU_OK;
+}

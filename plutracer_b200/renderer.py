@@ -1,0 +1,121 @@
+"""plu::renderer (reference inc/renderer.h:11-31) on the B200 through libplugpu's C ABI.
+
+    r = renderer(scene, None, (32, 32), stratified_sampler(tx.size, (n, n)), None)
+    r.render(tx)
+
+keeps the reference's constructor shape `renderer(surface* S, const camera& C, uvec2 tile_size,
+sampler* smp, const vector<shared_ptr<light>>& l)`.  On this side of the boundary the scene handle
+already carries camera, surfaces and lights (the flat tables), so `C` and `l` may be None; a
+CameraDesc passed as `C` overrides the scene's camera.  `tile_size` is accepted and ignored (the
+GPU path has no tiles).  There is no CPU fallback.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _ffi
+from .scene import Scene, stratified_sampler, texture2d  # noqa: F401  (re-exported)
+
+DEFAULT_SEED = 20261104
+
+
+class GpuContext:
+    """One libplugpu context = one CUDA device (one process per GPU)."""
+
+    def __init__(self, device=0):
+        self._lib = _ffi.lib()
+        self._h = C.c_void_p()
+        rc = self._lib.plu_gpu_create(int(device), C.byref(self._h))
+        if rc != _ffi.PLU_OK:
+            raise _ffi.PluError(rc, self._lib.plu_gpu_last_error(None).decode(errors="replace"))
+        self.device = int(device)
+        self._scene = None
+
+    def _check(self, rc):
+        if rc != _ffi.PLU_OK:
+            raise _ffi.PluError(rc, self._lib.plu_gpu_last_error(self._h).decode(errors="replace"))
+
+    def upload(self, scene):
+        self._check(self._lib.plu_gpu_upload_scene(self._h, scene.desc_ptr))
+        self._scene = scene
+
+    @staticmethod
+    def params(width, height, n_strata, seed=DEFAULT_SEED, flags=0, max_vertices=8, sample_begin=0, sample_stride=1,
+               sample_count=0, strata_per_wave=0):
+        p = _ffi.RenderParams()
+        p.width, p.height, p.n_strata, p.max_vertices = int(width), int(height), int(n_strata), int(max_vertices)
+        p.seed, p.flags = int(seed), int(flags)
+        p.sample_begin, p.sample_stride, p.sample_count = int(sample_begin), int(sample_stride), int(sample_count)
+        p.strata_per_wave = int(strata_per_wave)
+        return p
+
+    def render(self, params, out_rgb):
+        """renderer::render into a host float32 (H, W, 3) array, accumulating (+=)."""
+        assert out_rgb.dtype == np.float32 and out_rgb.flags.c_contiguous and out_rgb.size == params.width * params.height * 3
+        st = _ffi.RenderStats()
+        self._check(self._lib.plu_gpu_render(self._h, C.byref(params), out_rgb.ctypes.data, C.byref(st)))
+        return st
+
+    def render_device(self, params, device_ptr, stream=None):
+        """Same, into a device float buffer (e.g. a torch tensor's data_ptr()) on `stream`."""
+        st = _ffi.RenderStats()
+        self._check(self._lib.plu_gpu_render_device(self._h, C.byref(params), C.c_void_p(int(device_ptr)),
+                                                    C.c_void_p(int(stream) if stream else None), C.byref(st)))
+        return st
+
+    def trace_primary(self, width, height, flags=0):
+        n = width * height
+        ids, t, nrm = np.zeros(n, np.int32), np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        self._check(self._lib.plu_gpu_trace_primary(self._h, width, height, flags, ids.ctypes.data, t.ctypes.data, nrm.ctypes.data))
+        return ids, t, nrm
+
+    def trace_rays(self, origins, dirs, flags=0):
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        n = o.shape[0]
+        ids, t, nrm = np.zeros(n, np.int32), np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+        self._check(self._lib.plu_gpu_trace_rays(self._h, n, o.ctypes.data, d.ctypes.data, flags, ids.ctypes.data, t.ctypes.data, nrm.ctypes.data))
+        return ids, t, nrm
+
+    def sample_radiance(self, params, pixel_begin, pixel_count):
+        count = params.sample_count if params.sample_count > 0 else params.n_strata ** 2
+        out = np.zeros((pixel_count, count, 3), np.float32)
+        self._check(self._lib.plu_gpu_sample_radiance(self._h, C.byref(params), pixel_begin, pixel_count, out.ctypes.data))
+        return out
+
+    def close(self):
+        if self._h:
+            self._lib.plu_gpu_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class renderer:
+    """Drop-in for plu::renderer: same constructor shape, same render(target) call."""
+
+    def __init__(self, S, C_=None, tile_size=(32, 32), smp=None, l=None, device=0, seed=DEFAULT_SEED, flags=0):
+        if not isinstance(S, Scene):
+            raise TypeError("S must be a plutracer_b200.Scene (the flattened surface graph)")
+        if smp is None:
+            raise ValueError("renderer needs a sampler (sample_count gives the strata per pixel)")
+        self.scene, self.cam, self.tile_size, self.main_sampler, self.lights = S, C_, tuple(tile_size), smp, l
+        self.seed, self.flags = seed, flags
+        self.ctx = GpuContext(device)
+        self.last_stats = None
+
+    def render(self, target):
+        W, H = target.size
+        sc = self.scene
+        if self.cam is not None:   # a camera passed explicitly replaces the scene's
+            d = _ffi.SceneDesc.from_buffer_copy(sc.desc)
+            d.cam = self.cam
+            sc = Scene.from_desc(d, W, H, self.main_sampler.sample_count[0])
+        self.ctx.upload(sc)
+        p = GpuContext.params(W, H, self.main_sampler.sample_count[0], self.seed, self.flags)
+        self.last_stats = self.ctx.render(p, target.pixels)
+        return self.last_stats

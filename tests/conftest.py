@@ -1,0 +1,37 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def lib():
+    """libplugpu.so, built in-tree (nvcc cross-compiles without a GPU)."""
+    from plutracer_b200 import _ffi, build_lib
+    build_lib()
+    return _ffi.lib()
+
+
+@pytest.fixture(scope="session")
+def oracle(lib):
+    from tests.orc import Oracle
+    return Oracle()
+
+
+@pytest.fixture(scope="session")
+def gpu(lib):
+    from plutracer_b200 import GpuContext
+    ctx = GpuContext(0)   # raises PLU_E_CUDA without a device: no fallback
+    yield ctx
+    ctx.close()
+
+
+SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]

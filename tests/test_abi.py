@@ -1,0 +1,68 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/plugpu.h declares, and the host-side scene plumbing works.  No compute calls."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from tests.orc import GOLDEN, ROOT, golden_scene
+
+
+def test_header_symbols_all_exported(lib):
+    from plutracer_b200 import _ffi
+    hdr = open(os.path.join(ROOT, "include", "plugpu.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(plu_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 18
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in plugpu.h but not exported by libplugpu.so"
+    assert declared == set(_ffi.SYMBOLS), declared ^ set(_ffi.SYMBOLS)
+    assert lib.plu_abi_version() == 1
+
+
+def test_struct_sizes_match_header(lib):
+    from plutracer_b200 import _ffi
+    assert C.sizeof(_ffi.CameraDesc) == 17 * 4
+    assert C.sizeof(_ffi.MaterialDesc) == 13 * 4
+    assert C.sizeof(_ffi.TextureDesc) == 12 * 4
+    assert C.sizeof(_ffi.LightDesc) == 10 * 4
+    assert C.sizeof(_ffi.RenderParams) == 48
+    assert C.sizeof(_ffi.RenderStats) == 112
+
+
+def test_no_cpu_fallback(lib):
+    """Without a device plu_gpu_create must fail with PLU_E_CUDA (this test only runs its assertion on CPU boxes)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from plutracer_b200 import GpuContext, _ffi
+    with pytest.raises(_ffi.PluError) as e:
+        GpuContext(0)
+    assert e.value.code == -2
+
+
+def test_flat_scene_round_trip(lib, tmp_path):
+    sc = golden_scene("cornell-box")
+    assert sc.n_prims == 8 and sc.n_lights == 1 and sc.defaults == (512, 512, 8)
+    p = tmp_path / "x.pluscene"
+    sc.save_flat(p)
+    assert open(p, "rb").read() == open(os.path.join(GOLDEN, "cornell-box.pluscene"), "rb").read()
+    sc.override(1024, 256, 64)
+    assert sc.defaults == (1024, 256, 64)
+    assert sc.desc.cam.inv_image_size[0] == np.float32(1) / np.float32(1024)
+    assert sc.desc.cam.inv_image_size[1] == np.float32(1) / np.float32(256)
+
+
+def test_bad_inputs_rejected(lib, tmp_path):
+    from plutracer_b200 import Scene, _ffi
+    with pytest.raises(_ffi.PluError):
+        Scene.load_flat(tmp_path / "missing.pluscene")
+    bad = tmp_path / "bad.pluscene"
+    bad.write_bytes(b"not a scene")
+    with pytest.raises(_ffi.PluError):
+        Scene.load_flat(bad)
+    d = _ffi.SceneDesc()
+    d.abi_version = 99
+    assert lib.plu_scene_save_flat(C.byref(d), 1, 1, 1, b"/tmp/x") == -1
