@@ -272,7 +272,7 @@ def main():
         }
         ms = {"k_extend": ps.ms_extend, "k_shade": ps.ms_shade, "k_connect": ps.ms_connect}
         dom = max(ms, key=ms.get)
-        n_dom = 8 * (ps.kernel_launches - 0) // 26 if ps.kernel_launches else 1
+        n_dom = int(ps.waves) * 8 * (2 if dom == "k_shade" else 1)   # launches of that kernel class in the profiled pass
         achieved = alg[dom] / (ms[dom] * 1e-3) / 1e9 if ms[dom] > 0 else 0.0
         bytes_per_sample = (alg["k_extend"] + alg["k_shade"] + alg["k_connect"]) / max(ps.samples, 1) + 12.0
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,

@@ -172,6 +172,7 @@ typedef struct plu_render_stats {
 	double   ms_accumulate;
 	uint64_t shade_vertices;       /* path vertices shaded (= extension rays that hit)          */
 	uint64_t shadow_entries;       /* shaded vertices that needed a connection                  */
+	uint64_t waves;                /* waves (batches of paths in flight) this call ran          */
 } plu_render_stats;
 
 typedef struct plu_gpu_ctx plu_gpu_ctx;

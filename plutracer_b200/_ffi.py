@@ -61,7 +61,7 @@ class RenderStats(C.Structure):
                 ("bvh_nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64), ("ms_device", C.c_double),
                 ("ms_extend", C.c_double), ("ms_shade", C.c_double), ("ms_connect", C.c_double),
                 ("kernel_launches", C.c_uint64), ("ms_generate", C.c_double), ("ms_accumulate", C.c_double),
-                ("shade_vertices", C.c_uint64), ("shadow_entries", C.c_uint64)]
+                ("shade_vertices", C.c_uint64), ("shadow_entries", C.c_uint64), ("waves", C.c_uint64)]
 
 
 # every symbol include/plugpu.h declares: name -> (restype, argtypes)

@@ -14,7 +14,8 @@ namespace plud {
 
 // Reference-topology BVH node (bvh_tree.cpp:7-36), pre-order, stackless:
 //   lo = (min.xyz, skip)   hi = (max.xyz, prim)      prim >= 0: leaf (no bounds test, bvh_tree.cpp:40)
-// `skip` = index of the next node in pre-order that is NOT in this node's subtree.
+// `skip` = index of the next node in pre-order that is NOT in this node's subtree; in a leaf (whose
+// successor is the next index anyway) the field holds the surface kind (PLU_PRIM_*).
 struct ref_node { float4 lo, hi; };
 
 // Tight two-child node of the fast BVH (host/bvh_build.cpp), 64 B = four 128-bit loads:
@@ -34,6 +35,7 @@ struct scene_ref {
 	const fast_node* fast_nodes;    // null: traverse the reference tree
 	const int32_t* fast_prim_index; // leaf slots -> prim ids
 	int32_t n_fast_nodes;
+	int32_t has_spheres;
 	plu_camera_desc cam;
 
 	PLU_DEV const ref_node* ref_nodes() const { return (const ref_node*)(blob + off_ref_nodes); }

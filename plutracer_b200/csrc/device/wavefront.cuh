@@ -27,11 +27,26 @@ struct wave_buffers {
 	float4* thr[2];       // path_throughput, ping-pong by bounce parity
 	float4* rad;          // L
 	uint32_t* queue[2];   // extend queues, ping-pong
-	uint32_t* q_hit;      // paths whose extension ray hit
+	uint32_t* q_hit[2];   // paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR)
 	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
-	uint32_t* counters;   // [bounce*4 + {0: extend, 1: hit, 2: shadow}]
+	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_HIT_DIFFUSE, CNT_SHADOW, CNT_HIT_SPECULAR}]
 	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries
 };
+
+#define CNT_STRIDE 4
+#define CNT_EXTEND 0
+#define CNT_HIT_DIFFUSE 1
+#define CNT_SHADOW 2
+#define CNT_HIT_SPECULAR 3
+
+// Material classes: extend sorts the hits so that each shade launch runs one code path.
+//   CLS_DIFFUSE   diffuse_material: NEE (light + BSDF sampling, MIS) and a Lambert continuation
+//   CLS_SPECULAR  perfect_reflection / perfect_refraction / glass: every component is specular, so
+//                 bsdf::F == 0 and bsdf::sampleF(all & ~specular) has no matching component: the NEE
+//                 term is identically zero (renderer.cpp:11-12,31-32) and only the continuation is left
+//   emission      empty bsdf: Le, then the path ends (sampleF: pdf = 0) — done inside k_extend
+#define CLS_DIFFUSE 0
+#define CLS_SPECULAR 1
 
 #define FLAG_SPEC 1      // spec_bounce (renderer.cpp:79)
 #define FLAG_NONFINITE 2 // path_throughput holds an inf/NaN: `L += T * 0` terms are no longer no-ops
@@ -100,27 +115,48 @@ template <bool SMEM, bool COUNT>
 __global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce, uint32_t n_identity) {
 	scene_ref sc = sc_in;
 	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
-	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * 4 + 0];
+	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	const uint32_t* q = wb.queue[bounce & 1];
-	uint32_t* cnt_hit = wb.counters + bounce * 4 + 1;
+	uint32_t* cnt_diffuse = wb.counters + bounce * CNT_STRIDE + CNT_HIT_DIFFUSE;
+	uint32_t* cnt_specular = wb.counters + bounce * CNT_STRIDE + CNT_HIT_SPECULAR;
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 0, (unsigned long long)n);
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	const uint32_t lane = threadIdx.x & 31u;
+	const float nl = (float)sc.n_lights;
 	for (uint32_t j0 = blockIdx.x * blockDim.x + threadIdx.x - lane; j0 < n; j0 += gridDim.x * blockDim.x) {
 		uint32_t j = j0 + lane;
-		bool active = j < n, hit = false;
+		bool active = j < n, to_diffuse = false, to_specular = false;
 		uint32_t slot = 0;
 		if (active) {
 			slot = bounce == 0 ? j : q[j];
 			float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
 			ray r; r.e = mk3(o); r.d = mk3(d);
+			int flags = __float_as_int(d.w);
 			float t; int32_t prim;
-			hit = trace_scene<COUNT>(sc, r, o.w, t, prim, &tc);
-			if (hit) wb.hit[slot] = make_int2(__float_as_int(t), prim);
-			else {
+			if (trace_scene<COUNT>(sc, r, o.w, t, prim, &tc)) {
+				int4 meta = sc.prim_meta(prim);   // kind, material, light, tie rank
+				int32_t mtag = sc.material(meta.y).tag;
+				if (mtag == PLU_MAT_EMISSION) {
+					// emission_material: the vertex adds Le (first vertex / after a specular bounce, renderer.cpp:66),
+					// its empty bsdf gives NEE = 0 and sampleF pdf = 0, i.e. the path ends here (renderer.cpp:78)
+					bool le = bounce == 0 || (flags & FLAG_SPEC);
+					if (le || (flags & FLAG_NONFINITE)) {
+						f3 T = bounce == 0 ? mk3(1.f) : mk3(wb.thr[bounce & 1][slot]);
+						f3 L = mk3(wb.rad[slot]);
+						if (le) {
+							hit_rec hr; fill_record(sc, prim, meta.x, r, t, false, hr);
+							L = L + T * area_L(sc.light(meta.z), hr.norm, -r.d);
+						}
+						if (flags & FLAG_NONFINITE) L = L + T * (nl * mk3(0.f));
+						wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+					}
+				} else {
+					wb.hit[slot] = make_int2(__float_as_int(t), prim);
+					to_diffuse = mtag == PLU_MAT_DIFFUSE; to_specular = !to_diffuse;
+				}
+			} else {
 				// renderer.cpp:87-90: after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
 				// a no-op unless T is not finite
-				int flags = __float_as_int(d.w);
 				if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
 					f3 T = mk3(wb.thr[bounce & 1][slot]); f3 L = mk3(wb.rad[slot]);
 					for (int32_t i = 0; i < sc.n_lights; ++i) L = L + T * mk3(0.f);
@@ -128,8 +164,10 @@ __global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_re
 				}
 			}
 		}
-		uint32_t at = queue_push(cnt_hit, hit);
-		if (hit) wb.q_hit[at] = slot;
+		uint32_t at = queue_push(cnt_diffuse, to_diffuse);
+		if (to_diffuse) wb.q_hit[CLS_DIFFUSE][at] = slot;
+		at = queue_push(cnt_specular, to_specular);
+		if (to_specular) wb.q_hit[CLS_SPECULAR][at] = slot;
 	}
 	if (COUNT) {
 		unsigned long long a = tc.nodes, b = tc.prims;
@@ -140,15 +178,17 @@ __global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_re
 
 // ---- k_shade --------------------------------------------------------------------------------------------------
 // One path vertex: everything renderer.cpp:66-83 does between two scene->hit calls, except the
-// visibility tests of estimate_direct_light, which become shadow entries for k_connect.
-template <bool SMEM>
+// visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
+// instantiation per material class; the queue it reads holds only vertices of that class.
+template <bool SMEM, int CLS>
 __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
 	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
-	const uint32_t n = wb.counters[bounce * 4 + 1];
+	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
-	uint32_t* cnt_shadow = wb.counters + bounce * 4 + 2;
-	uint32_t* cnt_next = wb.counters + (bounce + 1) * 4 + 0;
+	const uint32_t* q_in = wb.q_hit[CLS];
+	uint32_t* cnt_shadow = wb.counters + bounce * CNT_STRIDE + CNT_SHADOW;
+	uint32_t* cnt_next = wb.counters + (bounce + 1) * CNT_STRIDE + CNT_EXTEND;
 	uint32_t* q_next = wb.queue[(bounce + 1) & 1];
 	const float4* thr_in = wb.thr[bounce & 1];
 	float4* thr_out = wb.thr[(bounce + 1) & 1];
@@ -160,31 +200,33 @@ __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref
 		uint32_t slot = 0, sh_flags = 0;
 		f3 p = mk3(0.f), wi1 = mk3(0.f), c1 = mk3(0.f), wi2 = mk3(0.f), c2 = mk3(0.f);
 		if (active) {
-			slot = wb.q_hit[j];
+			slot = q_in[j];
 			float4 o4 = wb.ray_o[slot], d4 = wb.ray_d[slot];
 			int2 h = wb.hit[slot];
 			ray r; r.e = mk3(o4); r.d = mk3(d4);
 			int flags = __float_as_int(d4.w);
 			float t = __int_as_float(h.x); int32_t prim = h.y;
-			int4 meta = sc.prim_meta(prim);   // tag, material, light, -
+			int4 meta = sc.prim_meta(prim);   // kind, material, light (-1 here: emissive hits end in k_extend), tie rank
 			const plu_material_desc& m = sc.material(meta.y);
 			hit_rec hr; fill_record(sc, prim, meta.x, r, t, m.texture >= 0, hr);
 			f3 T = bounce == 0 ? mk3(1.f) : mk3(thr_in[slot]);
 			philox_key key; int32_t px_x, px_y, s;
 			slot_to_path(w, slot, key, px_x, px_y, s);
-			vertex_rng rng; rng.begin(key, bounce);
+			vertex_rng rng;
+			if (CLS == CLS_DIFFUSE) rng.begin(key, bounce);
+			else rng.c = philox_call(key, 3u + 3u * (uint32_t)bounce);   // only the continuation draws are read
 			p = ray_at(r, t);
 			f3 nrm = hr.norm, wo = -r.d;
-			// renderer.cpp:66: emitted light at the first vertex or after a specular bounce
-			if ((bounce == 0 || (flags & FLAG_SPEC)) && (meta.z >= 0 || (flags & FLAG_NONFINITE))) {
-				f3 Le = meta.z >= 0 ? area_L(sc.light(meta.z), nrm, -r.d) : mk3(0.f);
+			// renderer.cpp:66: `L += T * Le` with Le == 0 on a non-emissive surface: only observable when T is not finite
+			if ((bounce == 0 || (flags & FLAG_SPEC)) && (flags & FLAG_NONFINITE)) {
 				f3 L = mk3(wb.rad[slot]);
-				L = L + T * Le;
+				L = L + T * mk3(0.f);
 				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 			}
 			bsdf b; make_bsdf(sc, m, hr, b);
+			if (CLS == CLS_DIFFUSE) b.tag = PLU_MAT_DIFFUSE;   // compile-time constant for everything below
 			// renderer.cpp:53-57 + :5-51 up to the visibility tests
-			if (sc.n_lights > 0) {
+			if (CLS == CLS_DIFFUSE && sc.n_lights > 0) {
 				int32_t li = (int32_t)gmin(floorf(rng.light_pick() * nl), nl - 1.f);
 				const plu_light_desc& l = sc.light(li);
 				bool is_delta = l.tag == PLU_LIGHT_POINT;
@@ -258,14 +300,16 @@ __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref
 				}
 			}
 		}
-		uint32_t at = queue_push(cnt_shadow, need_entry);
-		if (need_entry) {
-			wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
-			wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
-			wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
-			if (sh_flags & SH_NEED2) {
-				wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
-				wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
+		if (CLS == CLS_DIFFUSE) {
+			uint32_t at = queue_push(cnt_shadow, need_entry);
+			if (need_entry) {
+				wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
+				wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
+				wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
+				if (sh_flags & SH_NEED2) {
+					wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
+					wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
+				}
 			}
 		}
 		uint32_t an = queue_push(cnt_next, go_on);
@@ -280,7 +324,7 @@ template <bool SMEM, bool COUNT>
 __global__ void __launch_bounds__(256) k_connect(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
 	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
-	const uint32_t n = wb.counters[bounce * 4 + 2];
+	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
 	const float4* thr_in = wb.thr[bounce & 1];
 	const float nl = (float)sc.n_lights;

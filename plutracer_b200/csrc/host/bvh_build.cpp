@@ -62,7 +62,9 @@ box3 emit_ref(const plu_scene_desc* d, const std::vector<int32_t>& dfs, size_t l
 		out[me].prim = -1;
 	}
 	for (int i = 0; i < 3; ++i) { out[me].lo[i] = b.mn[i]; out[me].hi[i] = b.mx[i]; }
-	out[me].skip = (int32_t)out.size();
+	// interior: index of the next node outside this subtree; leaf (whose successor is always me + 1):
+	// the surface kind, so the walk needs no second lookup
+	out[me].skip = out[me].prim >= 0 ? d->prim_tag[out[me].prim] : (int32_t)out.size();
 	return b;
 }
 

@@ -31,6 +31,7 @@ struct plu_gpu_ctx {
 	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr;
 	bool blob_in_smem = false;
 	bool use_fast = false;
+	bool has_specular = false;     // any perfect-reflection / perfect-refraction / glass material
 	int32_t fast_threshold = 64;   // scenes with more surfaces than this use the fast BVH by default
 	// wave buffers
 	uint32_t capacity = 0;         // path slots
@@ -146,6 +147,7 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 	sc.n_ref_nodes = (int32_t)ref_nodes.size();
 	sc.n_prims = d->n_prims; sc.n_materials = d->n_materials; sc.n_textures = d->n_textures; sc.n_lights = d->n_lights;
 	sc.cam = d->cam;
+	for (size_t s = 0; s < n; ++s) if (d->prim_tag[s] == PLU_PRIM_SPHERE) sc.has_spheres = 1;
 	CU(cudaMalloc(&ctx->d_blob, blob.size()));
 	CU(cudaMemcpy(ctx->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
 	sc.blob = ctx->d_blob;
@@ -169,6 +171,8 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 	}
 	sc.fast_nodes = use_fast ? ctx->d_fast : nullptr;
 	ctx->use_fast = use_fast;
+	ctx->has_specular = false;
+	for (int32_t i = 0; i < d->n_materials; ++i) if (d->materials[i].tag >= PLU_MAT_PERFECT_REFLECTION && d->materials[i].tag <= PLU_MAT_GLASS) ctx->has_specular = true;
 	sc.fast_prim_index = ctx->d_fast_index;
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
@@ -189,7 +193,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	CU(cudaFree(ctx->d_wave_mem)); ctx->d_wave_mem = nullptr; ctx->capacity = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = 10 * al(N * 16) + al(N * 8) + 3 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
+	size_t bytes = 10 * al(N * 16) + al(N * 8) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
 	CU(cudaMalloc(&ctx->d_wave_mem, bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave_mem;
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
@@ -200,7 +204,8 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	wb.sh_p = (float4*)take(N * 16); wb.sh_w1 = (float4*)take(N * 16); wb.sh_c1 = (float4*)take(N * 16);
 	wb.sh_w2 = (float4*)take(N * 16); wb.sh_c2 = (float4*)take(N * 16);
 	wb.hit = (int2*)take(N * 8);
-	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4); wb.q_hit = (uint32_t*)take(N * 4);
+	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4);
+	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
 	if ((size_t)(p - (unsigned char*)ctx->d_wave_mem) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
@@ -215,7 +220,7 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 	return ctx->sm_count * occ;
 }
 
-struct launch_cfg { bool smem, count; size_t smem_bytes; int g_gen, g_ext, g_shade, g_conn, g_acc; };
+struct launch_cfg { bool smem, count; size_t smem_bytes; int g_gen, g_ext, g_shade[2], g_conn, g_acc; };
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
 	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.smem_bytes = c.smem ? ctx->sc.blob_bytes : 0;
@@ -226,7 +231,8 @@ static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
 	             : (count ? grid_for(ctx, K<false, true>, 0) : grid_for(ctx, K<false, false>, 0))
 	PICK(c.g_ext, k_extend); PICK(c.g_conn, k_connect);
 #undef PICK
-	c.g_shade = c.smem ? grid_for(ctx, k_shade<true>, c.smem_bytes) : grid_for(ctx, k_shade<false>, 0);
+	c.g_shade[0] = c.smem ? grid_for(ctx, k_shade<true, CLS_DIFFUSE>, c.smem_bytes) : grid_for(ctx, k_shade<false, CLS_DIFFUSE>, 0);
+	c.g_shade[1] = c.smem ? grid_for(ctx, k_shade<true, CLS_SPECULAR>, c.smem_bytes) : grid_for(ctx, k_shade<false, CLS_SPECULAR>, 0);
 	return c;
 }
 
@@ -255,7 +261,7 @@ struct wave_profiler {
 static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& w, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr) {
 	wave_buffers& wb = ctx->wb;
 	wave_profiler none; if (!pf) pf = &none;
-	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * 4 * sizeof(uint32_t), st);
+	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);
 	pf->mark(-1, st);
 	k_generate<<<c.g_gen, 256, 0, st>>>(sc, w, wb);
 	pf->mark(0, st);
@@ -265,7 +271,8 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			if (c.count) k_extend<true, true><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<true, false><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			k_shade<true><<<c.g_shade, 256, c.smem_bytes, st>>>(sc, w, wb, b);
+			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], 256, c.smem_bytes, st>>>(sc, w, wb, b);
+			if (ctx->has_specular) { k_shade<true, CLS_SPECULAR><<<c.g_shade[1], 256, c.smem_bytes, st>>>(sc, w, wb, b); launches++; }
 			pf->mark(2, st);
 			if (c.count) k_connect<true, true><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
 			else k_connect<true, false><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
@@ -274,7 +281,8 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			if (c.count) k_extend<false, true><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<false, false><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			k_shade<false><<<c.g_shade, 256, 0, st>>>(sc, w, wb, b);
+			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], 256, 0, st>>>(sc, w, wb, b);
+			if (ctx->has_specular) { k_shade<false, CLS_SPECULAR><<<c.g_shade[1], 256, 0, st>>>(sc, w, wb, b); launches++; }
 			pf->mark(2, st);
 			if (c.count) k_connect<false, true><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
 			else k_connect<false, false><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
@@ -329,7 +337,7 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
 	CU(cudaMemsetAsync(ctx->wb.stats, 0, 8 * sizeof(unsigned long long), st));
 	CU(cudaEventRecord(ctx->ev0, st));
-	uint64_t launches = 0, samples = 0;
+	uint64_t launches = 0, samples = 0, waves = 0;
 	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
 	// main image, then (compat) the overflow-column strip: sampler.h:74-78 renders x == W for rows 0..H-1
 	for (int pass = 0; pass < ((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? 2 : 1); ++pass) {
@@ -344,7 +352,7 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 				k_accumulate<<<cfg.g_acc, 256, 0, st>>>(w, ctx->wb, d_rgb, smp_wgt);
 				prof.mark(4, st); prof.collect(st);
 				launches++;
-				samples += w.n_slots;
+				samples += w.n_slots; waves++;
 			}
 			p0 += np;
 		}
@@ -360,7 +368,7 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 		stats->samples = samples; stats->rays_extend = h[0]; stats->rays_shadow = h[1];
 		stats->bvh_nodes_visited = h[2]; stats->prims_tested = h[3];
 		stats->ms_device = ms; stats->kernel_launches = launches;
-		stats->shade_vertices = h[4]; stats->shadow_entries = h[5];
+		stats->shade_vertices = h[4]; stats->shadow_entries = h[5]; stats->waves = waves;
 		stats->ms_generate = prof.ms[0]; stats->ms_extend = prof.ms[1]; stats->ms_shade = prof.ms[2];
 		stats->ms_connect = prof.ms[3]; stats->ms_accumulate = prof.ms[4];
 	}

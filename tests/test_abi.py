@@ -29,7 +29,7 @@ def test_struct_sizes_match_header(lib):
     assert C.sizeof(_ffi.TextureDesc) == 12 * 4
     assert C.sizeof(_ffi.LightDesc) == 10 * 4
     assert C.sizeof(_ffi.RenderParams) == 48
-    assert C.sizeof(_ffi.RenderStats) == 112
+    assert C.sizeof(_ffi.RenderStats) == 120
 
 
 def test_no_cpu_fallback(lib):
