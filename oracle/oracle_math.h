@@ -142,6 +142,10 @@ inline void philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t
 	}
 	out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
-inline float u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }  // [0,1), 24 bits
+// 32-bit word -> [0,1) exactly as libstdc++'s uniform_real_distribution<float> maps one mt19937 word
+// (generate_canonical<float,24>: float(x) / 2^32 rounded to nearest, a result of 1.0 stepped down to
+// nextafter(1, 0)), so the Philox stream has the reference's resolution near 0 — the estimator has 1/cos
+// singularities at the rim of the cosine-hemisphere warp and its tail depends on that resolution
+inline float u01(uint32_t x) { float u = (float)x * 2.3283064365386963e-10f; return u >= 1.f ? 0.99999994f : u; }
 
 }  // namespace orc

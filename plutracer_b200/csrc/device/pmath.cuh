@@ -127,7 +127,9 @@ PLU_DEV u4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uin
 	}
 	u4 o; o.x = c0; o.y = c1; o.z = c2; o.w = c3; return o;
 }
-PLU_DEV float u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }
+// one 32-bit word -> [0,1) the way libstdc++ maps an mt19937 word for the reference (cmmn.h:245-248:
+// uniform_real_distribution<float> = float(x) / 2^32, round to nearest, 1.0 stepped down)
+PLU_DEV float u01(uint32_t x) { float u = __uint2float_rn(x) * 2.3283064365386963e-10f; return u >= 1.f ? 0.99999994f : u; }
 
 struct philox_key { uint32_t pixel, sample, k0, k1; };
 PLU_DEV u4 philox_call(const philox_key& k, uint32_t call) { return philox4x32_10(k.pixel, k.sample, call, 0x504c5531u, k.k0, k.k1); }

@@ -77,15 +77,14 @@ def test_leaf_order_matches_reference_tree(oracle, name):
     assert np.array_equal(sc.reference_leaf_order(), ref_rank)   # the product's own restatement of the build
 
 
-@pytest.mark.parametrize("name", ["cornell-box", "refrac0"])
-def test_philox_stream_agrees_with_reference_stream(oracle, name):
-    """Same path code, the two random streams: means agree within Monte-Carlo error."""
+@pytest.mark.parametrize("name", ["refrac0", "room"])
+def test_philox_stream_converges_to_reference_renders(oracle, name):
+    """Same path code, the Philox stream instead of mt19937: 1024 spp at 128x96 against the two
+    independent-seed renders of the unmodified reference (the test the GPU path has to pass too)."""
     from plutracer_b200 import GpuContext
-    w, h, n = 16, 12, 8
+    from tests.metrics import check_converged, converged_metrics
+    g = np.load(os.path.join(GOLDEN, name + ".converged.npz"))
+    w, h, n = (int(v) for v in g["cfg"])
     sc = golden_scene(name, w, h, n)
-    p = GpuContext.params(w, h, n, seed=3)
-    a, _ = oracle.render(sc, p, trig=0, n_threads=4)
-    b, _ = oracle.render_mt(sc, w, h, n, 99, 0, 0, w, h, trig=1, per_sample=False)
-    ok = np.isfinite(a).all(axis=2) & np.isfinite(b).all(axis=2)
-    assert ok.mean() > 0.95
-    assert abs(a[ok].mean() - b[ok].mean()) < 0.1 * max(a[ok].mean(), 1e-3)
+    img, _ = oracle.render(sc, GpuContext.params(w, h, n, seed=424242, flags=1), trig=0)
+    check_converged(converged_metrics(img, g["a"], g["b"]), w * h)
