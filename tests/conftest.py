@@ -34,4 +34,6 @@ def gpu(lib):
     ctx.close()
 
 
-SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]
+REF_SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's scenes (BASELINE.json configs)
+OWN_SCENES = ["atrium", "colonnade", "shard"]                          # scenes/ of this repo
+SCENES = REF_SCENES + OWN_SCENES

@@ -29,15 +29,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "plu_ref")
 REF_SCENES = os.environ.get("PLU_REFERENCE", "/root/reference") + "/scenes"
-SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]
+SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's own scenes/ (BASELINE.json configs)
+OWN_SCENES = ["atrium", "colonnade", "shard"]   # this repo's scenes/: all material kinds, scripted objects + lens, triangle mesh
 PW, PH = 96, 72
 SW, SH, SN, SSEED = 32, 24, 2, 7
 
 
-def run(*args, env=None):
+def _run(*args, env=None, cwd=None):
     e = dict(os.environ)
     e.update(env or {})
-    res = subprocess.run([REF_BIN] + [str(a) for a in args], capture_output=True, text=True, env=e)
+    res = subprocess.run([REF_BIN] + [str(a) for a in args], capture_output=True, text=True, env=e, cwd=cwd)
     if res.returncode != 0:
         raise RuntimeError(f"plu_ref {args}: {res.stderr}")
     return res.stdout
@@ -80,8 +81,13 @@ def main():
     tmp = "/tmp/plu_golden"
     os.makedirs(tmp, exist_ok=True)
     rng = np.random.default_rng(20261104)
-    for s in SCENES:
-        urn = f"{REF_SCENES}/{s}.urn"
+    for s in SCENES + OWN_SCENES:
+        own = s in OWN_SCENES
+        urn = f"{ROOT}/scenes/{s}.urn" if own else f"{REF_SCENES}/{s}.urn"
+        cwd = f"{ROOT}/scenes" if own else None   # the reference opens triangle-mesh files relative to the cwd
+
+        def run(*a, env=None, _cwd=cwd):
+            return _run(*a, env=env, cwd=_cwd)
         run("dump-scene", urn, 0, 0, 0, f"{HERE}/{s}.pluscene")
         run("primary", urn, PW, PH, f"{tmp}/p.bin")
         pid, pt, pn = read_hits(f"{tmp}/p.bin", PW * PH)
@@ -107,10 +113,10 @@ def main():
                             rays_o=o, rays_d=d, rays_id=rid, rays_t=rt, rays_n=rn,
                             st_img=st_img, st_samples=st_smp, st_cfg=np.array([SW, SH, SN, SSEED]), x_first=np.array(0))
         print(s, "hits", float(hit.mean()), "ray hits", float((rid >= 0).mean()))
-        if args.converged:
+        if args.converged and not own:
             out = {}
             for tag, seed in (("a", 101), ("b", 202)):
-                js = run("render", urn, 128, 96, 32, f"{tmp}/c.bin", env={"PLU_SEED": str(seed)})
+                js = _run("render", urn, 128, 96, 32, f"{tmp}/c.bin", env={"PLU_SEED": str(seed)})
                 out[tag] = np.fromfile(f"{tmp}/c.bin", np.float32).reshape(96, 128, 3)
                 out[tag + "_info"] = np.array(json.dumps(json.loads(js.strip().splitlines()[-1])))
             np.savez_compressed(f"{HERE}/{s}.converged.npz", cfg=np.array([128, 96, 32]), **out)

@@ -5,7 +5,7 @@ import os
 import numpy as np
 import pytest
 
-from tests.conftest import SCENES
+from tests.conftest import REF_SCENES, SCENES
 from tests.orc import GOLDEN, golden_scene
 from tests.metrics import check_converged as _check_converged, converged_metrics as _converged_metrics
 from tests.test_oracle import bits, same_bits
@@ -112,7 +112,7 @@ def test_errors(gpu):
         gpu.sample_radiance(GpuContext.params(8, 8, 2, sample_begin=0, sample_stride=0, sample_count=3), 0, 4)
 
 
-@pytest.mark.parametrize("name", SCENES)
+@pytest.mark.parametrize("name", REF_SCENES)
 def test_converged_image_matches_reference_renders(gpu, name):
     """1024 spp at 128x96 against two independent-seed runs of the reference's multithreaded renderer::render
     (overflow-column quirk reproduced with PLU_RENDER_COMPAT_OVERFLOW_COLUMN so the full frame compares)."""
