@@ -129,3 +129,38 @@ class texture2d:
 
     def pixel(self, c):
         return self.pixels[c[1], c[0]]
+
+
+def scene_from_tables(cam, prim_tag, prim_material, prim_data, materials, lights, width, height, n_strata,
+                      textures=(), tri_uv=None, tri_normal=None, tie_rank=None):
+    """Build a Scene from numpy tables (the same tables the reference-side flattener fills):
+    prim_tag int32 [n], prim_material int32 [n], prim_data float32 [n, 12], materials / textures / lights
+    sequences of the _ffi *Desc structs; triangles need tri_uv [n, 6] and tri_normal [n, 9]."""
+    import numpy as np
+    n = len(prim_tag)
+    tag = np.ascontiguousarray(prim_tag, np.int32)
+    mat = np.ascontiguousarray(prim_material, np.int32)
+    data = np.ascontiguousarray(prim_data, np.float32).reshape(n, 12)
+    d = _ffi.SceneDesc()
+    d.abi_version = 1
+    d.cam = cam
+    d.n_prims, d.n_materials, d.n_textures, d.n_lights = n, len(materials), len(textures), len(lights)
+    fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    d.prim_tag, d.prim_material, d.prim_data = tag.ctypes.data_as(ip), mat.ctypes.data_as(ip), data.ctypes.data_as(fp)
+    keep = [tag, mat, data]
+    if tri_uv is not None:
+        uv = np.ascontiguousarray(tri_uv, np.float32).reshape(n, 6)
+        nr = np.ascontiguousarray(tri_normal, np.float32).reshape(n, 9)
+        d.prim_tri_uv, d.prim_tri_normal = uv.ctypes.data_as(fp), nr.ctypes.data_as(fp)
+        keep += [uv, nr]
+    if tie_rank is not None:
+        tr = np.ascontiguousarray(tie_rank, np.int32)
+        d.prim_tie_rank = tr.ctypes.data_as(ip)
+        keep.append(tr)
+    marr = (_ffi.MaterialDesc * max(len(materials), 1))(*materials)
+    tarr = (_ffi.TextureDesc * max(len(textures), 1))(*textures)
+    larr = (_ffi.LightDesc * max(len(lights), 1))(*lights)
+    d.materials, d.textures, d.lights = marr, tarr, larr
+    sc = Scene.from_desc(d, width, height, n_strata)   # deep copy: the numpy arrays may go away afterwards
+    del keep
+    return sc
