@@ -29,15 +29,17 @@ struct wave_buffers {
 	uint32_t* queue[2];   // extend queues, ping-pong
 	uint32_t* q_hit[2];   // paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR)
 	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
-	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_HIT_DIFFUSE, CNT_SHADOW, CNT_HIT_SPECULAR}]
+	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_SHADOW, CNT_HIT_DIFFUSE, CNT_HIT_SPECULAR}]
 	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries
 };
 
-#define CNT_STRIDE 4
+// one 128-byte line per bounce, one 32-byte sector per counter a kernel adds to; the two hit counters are
+// the halves of one 64-bit word so that k_extend adds to both with a single atomic
+#define CNT_STRIDE 32
 #define CNT_EXTEND 0
-#define CNT_HIT_DIFFUSE 1
-#define CNT_SHADOW 2
-#define CNT_HIT_SPECULAR 3
+#define CNT_SHADOW 8
+#define CNT_HIT_DIFFUSE 16
+#define CNT_HIT_SPECULAR 17
 
 // Material classes: extend sorts the hits so that each shade launch runs one code path.
 //   CLS_DIFFUSE   diffuse_material: NEE (light + BSDF sampling, MIS) and a Lambert continuation
@@ -76,17 +78,45 @@ PLU_DEV void slot_to_path(const wave_desc& w, uint32_t slot, philox_key& key, in
 	key.pixel = (uint32_t)pix; key.sample = (uint32_t)s; key.k0 = w.seed_lo; key.k1 = w.seed_hi;
 }
 
-// Warp-aggregated queue push: every lane of the warp must call it (converged).
-PLU_DEV uint32_t queue_push(uint32_t* counter, bool pred) {
-	unsigned mask = __ballot_sync(0xffffffffu, pred);
-	if (mask == 0) return 0;
-	unsigned lane = threadIdx.x & 31u;
-	int leader = __ffs(mask) - 1;
-	uint32_t base = 0;
-	if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
-	base = __shfl_sync(0xffffffffu, base, leader);
-	return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+// Queue pushes are aggregated in two levels.  ncu (profiles/r01b): with one global atomicAdd per warp
+// the ~1.2 G atomics/s that all land on the same counter paced k_extend (the shuffle that consumes the
+// atomic's result still stalled when it was issued a whole loop iteration earlier).  Now: warp ballot +
+// popc prefix -> one SHARED-memory atomic per warp -> one global atomic per CTA and loop iteration,
+// issued by thread 0 after a barrier and consumed one barrier later, so its round trip overlaps the
+// next block of work.  warp_tally() is the warp part; the CTA part is written out in each kernel.
+struct warp_tally {
+	uint32_t ofs;    // this lane's offset inside the CTA's batch (valid where pred was set)
+	PLU_DEV void add(uint32_t* s_counter, bool pred) {
+		unsigned mask = __ballot_sync(0xffffffffu, pred);
+		unsigned lane = threadIdx.x & 31u;
+		uint32_t w = 0;
+		if (mask != 0) {
+			if (lane == 0) w = atomicAdd(s_counter, (uint32_t)__popc(mask));
+			w = __shfl_sync(0xffffffffu, w, 0);
+		}
+		ofs = w + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+	}
+};
+
+// Per-thread asynchronous gathers into shared memory (LDGSTS): the inputs of the NEXT loop iteration
+// are fetched while the current one is traced / shaded, without holding registers.  Each thread only
+// ever reads the rows it copied itself, so cp.async.wait_group is the only synchronisation needed.
+PLU_DEV void cp_async_16(void* smem_dst, const void* gsrc) {
+	unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
 }
+PLU_DEV void cp_async_8(void* smem_dst, const void* gsrc) {
+	unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gsrc) : "memory");
+}
+PLU_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+#define PLU_CTA 256
+// staging bytes per kernel (two stages of per-thread rows), added to the scene blob in dynamic shared memory
+#define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)
+#define PLU_STAGE_SHADE (2 * (3 * PLU_CTA * 16 + PLU_CTA * 8))
+#define PLU_STAGE_CONNECT (2 * 5 * PLU_CTA * 16)
 
 extern __shared__ uint4 plu_smem[];
 
@@ -111,25 +141,58 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_
 }
 
 // ---- k_extend -------------------------------------------------------------------------------------------------
+// Loop skeleton shared by extend / shade / connect: iteration i computes on rows that were gathered
+// into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
+// the queue entry of iteration i+2; queue pushes started in iteration i are completed in iteration i+1.
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce, uint32_t n_identity) {
+__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce, uint32_t n_identity) {
 	scene_ref sc = sc_in;
-	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	unsigned char* stage_base = (unsigned char*)plu_smem;
+	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
+	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
+	float4* st_d = st_o + 2 * PLU_CTA;             // [2][PLU_CTA]
 	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	const uint32_t* q = wb.queue[bounce & 1];
 	uint32_t* cnt_diffuse = wb.counters + bounce * CNT_STRIDE + CNT_HIT_DIFFUSE;
 	uint32_t* cnt_specular = wb.counters + bounce * CNT_STRIDE + CNT_HIT_SPECULAR;
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 0, (unsigned long long)n);
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
-	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
 	const float nl = (float)sc.n_lights;
-	for (uint32_t j0 = blockIdx.x * blockDim.x + threadIdx.x - lane; j0 < n; j0 += gridDim.x * blockDim.x) {
-		uint32_t j = j0 + lane;
+	const bool ident = bounce == 0;
+
+	uint32_t j = blockIdx.x * PLU_CTA + tid;
+	uint32_t slot = 0, slot_next = 0;
+	if (j < n) {
+		slot = ident ? j : q[j];
+		cp_async_16(st_o + tid, wb.ray_o + slot); cp_async_16(st_d + tid, wb.ray_d + slot);
+	}
+	cp_async_commit();
+	if (j + stride < n) slot_next = ident ? j + stride : q[j + stride];
+	// CTA-level push state (see warp_tally): counts [3] rotate so that thread 0 can clear one while the
+	// warps already add to the next; s_base is double-buffered for the same reason
+	__shared__ uint32_t s_cnt[3][2];
+	__shared__ uint2 s_base[2];
+	if (tid < 6) (&s_cnt[0][0])[tid] = 0;
+	__syncthreads();
+	unsigned long long pending = 0;   // thread 0: result of the CTA's global atomic of the previous iteration
+	uint32_t pslot = 0, p_ofs_d = 0, p_ofs_s = 0; bool p_d = false, p_s = false;
+	uint32_t buf = 0, it = 0, k3 = 0;
+	unsigned long long* cnt_pair = (unsigned long long*)cnt_diffuse;   // (diffuse, specular) = (low, high)
+	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
+		const uint32_t jn = j + stride, jnn = jn + stride;
+		const bool has_next = jn < n;
+		if (has_next) {
+			cp_async_16(st_o + (buf ^ 1u) * PLU_CTA + tid, wb.ray_o + slot_next);
+			cp_async_16(st_d + (buf ^ 1u) * PLU_CTA + tid, wb.ray_d + slot_next);
+		}
+		cp_async_commit();
+		uint32_t slot_nn = 0;
+		if (has_next && jnn < n) slot_nn = ident ? jnn : q[jnn];
+		cp_async_wait<1>();
 		bool active = j < n, to_diffuse = false, to_specular = false;
-		uint32_t slot = 0;
 		if (active) {
-			slot = bounce == 0 ? j : q[j];
-			float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
+			float4 o = st_o[buf * PLU_CTA + tid], d = st_d[buf * PLU_CTA + tid];
 			ray r; r.e = mk3(o); r.d = mk3(d);
 			int flags = __float_as_int(d.w);
 			float t; int32_t prim;
@@ -164,10 +227,30 @@ __global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_re
 				}
 			}
 		}
-		uint32_t at = queue_push(cnt_diffuse, to_diffuse);
-		if (to_diffuse) wb.q_hit[CLS_DIFFUSE][at] = slot;
-		at = queue_push(cnt_specular, to_specular);
-		if (to_specular) wb.q_hit[CLS_SPECULAR][at] = slot;
+		warp_tally td, ts; td.add(&s_cnt[k3][0], to_diffuse); ts.add(&s_cnt[k3][1], to_specular);
+		if (tid == 0 && it > 0) s_base[(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
+		__syncthreads();
+		if (it > 0) {   // the previous iteration's entries: its global base has arrived meanwhile
+			uint2 gb = s_base[(it - 1u) & 1u];
+			if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
+			if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
+		}
+		if (tid == 0) {
+			uint32_t cd = s_cnt[k3][0], cs = s_cnt[k3][1];
+			pending = (cd | cs) ? atomicAdd(cnt_pair, ((unsigned long long)cs << 32) | cd) : 0ull;
+			uint32_t kz = k3 == 0 ? 2u : k3 - 1u;   // (it + 2) % 3: idle until the iteration after next
+			s_cnt[kz][0] = 0; s_cnt[kz][1] = 0;
+		}
+		p_d = to_diffuse; p_s = to_specular; p_ofs_d = td.ofs; p_ofs_s = ts.ofs; pslot = slot;
+		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u;
+		it++; k3 = k3 == 2 ? 0u : k3 + 1u;
+	}
+	if (it > 0) {
+		if (tid == 0) s_base[(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
+		__syncthreads();
+		uint2 gb = s_base[(it - 1u) & 1u];
+		if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
+		if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
 	}
 	if (COUNT) {
 		unsigned long long a = tc.nodes, b = tc.prims;
@@ -181,9 +264,14 @@ __global__ void __launch_bounds__(256) k_extend(const __grid_constant__ scene_re
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
-	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	unsigned char* stage_base = (unsigned char*)plu_smem;
+	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
+	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
+	float4* st_d = st_o + 2 * PLU_CTA;
+	float4* st_T = st_d + 2 * PLU_CTA;
+	int2* st_h = (int2*)(st_T + 2 * PLU_CTA);
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
 	const uint32_t* q_in = wb.q_hit[CLS];
@@ -192,38 +280,66 @@ __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref
 	uint32_t* q_next = wb.queue[(bounce + 1) & 1];
 	const float4* thr_in = wb.thr[bounce & 1];
 	float4* thr_out = wb.thr[(bounce + 1) & 1];
-	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
 	const float nl = (float)sc.n_lights;
-	for (uint32_t j0 = blockIdx.x * blockDim.x + threadIdx.x - lane; j0 < n; j0 += gridDim.x * blockDim.x) {
-		uint32_t j = j0 + lane;
+	const bool first = bounce == 0;
+
+	auto gather = [&](uint32_t b, uint32_t sl) {
+		cp_async_16(st_o + b * PLU_CTA + tid, wb.ray_o + sl); cp_async_16(st_d + b * PLU_CTA + tid, wb.ray_d + sl);
+		cp_async_8(st_h + b * PLU_CTA + tid, wb.hit + sl);
+		if (!first) cp_async_16(st_T + b * PLU_CTA + tid, thr_in + sl);
+	};
+	uint32_t j = blockIdx.x * PLU_CTA + tid;
+	uint32_t slot = 0, slot_next = 0;
+	if (j < n) { slot = q_in[j]; gather(0, slot); }
+	cp_async_commit();
+	if (j + stride < n) slot_next = q_in[j + stride];
+	// CTA-level push state: the shadow-queue batch is reserved and written within the iteration (two
+	// barriers apart, the continuation is sampled in between); the next-queue batch is completed in the
+	// following iteration
+	__shared__ uint32_t s_sh_cnt[2], s_n_cnt[2], s_sh_base, s_n_base[2];
+	if (tid < 2) { s_sh_cnt[tid] = 0; s_n_cnt[tid] = 0; }
+	__syncthreads();
+	uint32_t pending_sh = 0, pending_n = 0;   // thread 0
+	uint32_t pslot = 0, p_ofs_n = 0, buf = 0, it = 0; bool p_go = false;
+	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
+		const uint32_t jn = j + stride, jnn = jn + stride;
+		const bool has_next = jn < n;
+		if (has_next) gather(buf ^ 1u, slot_next);
+		cp_async_commit();
+		uint32_t slot_nn = 0;
+		if (has_next && jnn < n) slot_nn = q_in[jnn];
+		cp_async_wait<1>();
 		bool active = j < n, need_entry = false, go_on = false;
-		uint32_t slot = 0, sh_flags = 0;
+		uint32_t sh_flags = 0;
 		f3 p = mk3(0.f), wi1 = mk3(0.f), c1 = mk3(0.f), wi2 = mk3(0.f), c2 = mk3(0.f);
+		f3 T = mk3(1.f), nrm = mk3(0.f), wo = mk3(0.f);
+		float t = 0.f; int flags = 0;
+		bsdf b; vertex_rng rng;
+		b.tag = PLU_MAT_DIFFUSE;
 		if (active) {
-			slot = q_in[j];
-			float4 o4 = wb.ray_o[slot], d4 = wb.ray_d[slot];
-			int2 h = wb.hit[slot];
+			float4 o4 = st_o[buf * PLU_CTA + tid], d4 = st_d[buf * PLU_CTA + tid];
+			int2 h = st_h[buf * PLU_CTA + tid];
 			ray r; r.e = mk3(o4); r.d = mk3(d4);
-			int flags = __float_as_int(d4.w);
-			float t = __int_as_float(h.x); int32_t prim = h.y;
+			flags = __float_as_int(d4.w);
+			t = __int_as_float(h.x); int32_t prim = h.y;
 			int4 meta = sc.prim_meta(prim);   // kind, material, light (-1 here: emissive hits end in k_extend), tie rank
 			const plu_material_desc& m = sc.material(meta.y);
 			hit_rec hr; fill_record(sc, prim, meta.x, r, t, m.texture >= 0, hr);
-			f3 T = bounce == 0 ? mk3(1.f) : mk3(thr_in[slot]);
+			if (!first) T = mk3(st_T[buf * PLU_CTA + tid]);
 			philox_key key; int32_t px_x, px_y, s;
 			slot_to_path(w, slot, key, px_x, px_y, s);
-			vertex_rng rng;
 			if (CLS == CLS_DIFFUSE) rng.begin(key, bounce);
 			else rng.c = philox_call(key, 3u + 3u * (uint32_t)bounce);   // only the continuation draws are read
 			p = ray_at(r, t);
-			f3 nrm = hr.norm, wo = -r.d;
+			nrm = hr.norm; wo = -r.d;
 			// renderer.cpp:66: `L += T * Le` with Le == 0 on a non-emissive surface: only observable when T is not finite
 			if ((bounce == 0 || (flags & FLAG_SPEC)) && (flags & FLAG_NONFINITE)) {
 				f3 L = mk3(wb.rad[slot]);
 				L = L + T * mk3(0.f);
 				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 			}
-			bsdf b; make_bsdf(sc, m, hr, b);
+			make_bsdf(sc, m, hr, b);
 			if (CLS == CLS_DIFFUSE) b.tag = PLU_MAT_DIFFUSE;   // compile-time constant for everything below
 			// renderer.cpp:53-57 + :5-51 up to the visibility tests
 			if (CLS == CLS_DIFFUSE && sc.n_lights > 0) {
@@ -286,34 +402,57 @@ __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref
 				L = L + T * (nl * mk3(0.f));
 				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 			}
-			// renderer.cpp:76-83: continuation
-			if (bounce < w.max_vertices - 1) {
-				uint32_t types = 0; float pdf; f3 wi;
-				f3 f = b.sampleF(rng, 1, nrm, wo, wi, pdf, BX_ALL, types);
-				if (!(dot(f, f) == 0.f || pdf == 0.f)) {
-					T = T * (f * fabsf(dot(wi, nrm)) / pdf);
-					int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
-					wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
-					wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
-					thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
-					go_on = true;
-				}
+		}
+		// barrier 1: shadow batch counted; previous iteration's next-queue base published
+		warp_tally tsh; tsh.ofs = 0;
+		if (CLS == CLS_DIFFUSE) tsh.add(&s_sh_cnt[it & 1u], need_entry);
+		if (tid == 0 && it > 0) s_n_base[(it - 1u) & 1u] = pending_n;
+		__syncthreads();
+		if (it > 0 && p_go) q_next[s_n_base[(it - 1u) & 1u] + p_ofs_n] = pslot;
+		if (CLS == CLS_DIFFUSE && tid == 0) {   // the global atomic travels while the continuation is sampled
+			uint32_t c = s_sh_cnt[it & 1u];
+			pending_sh = c ? atomicAdd(cnt_shadow, c) : 0u;
+			s_sh_cnt[(it + 1u) & 1u] = 0;
+		}
+		// renderer.cpp:76-83: continuation
+		if (active && bounce < w.max_vertices - 1) {
+			uint32_t types = 0; float pdf; f3 wi;
+			f3 f = b.sampleF(rng, 1, nrm, wo, wi, pdf, BX_ALL, types);
+			if (!(dot(f, f) == 0.f || pdf == 0.f)) {
+				T = T * (f * fabsf(dot(wi, nrm)) / pdf);
+				int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
+				wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
+				wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
+				thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
+				go_on = true;
 			}
 		}
-		if (CLS == CLS_DIFFUSE) {
-			uint32_t at = queue_push(cnt_shadow, need_entry);
-			if (need_entry) {
-				wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
-				wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
-				wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
-				if (sh_flags & SH_NEED2) {
-					wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
-					wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
-				}
+		// barrier 2: next-queue batch counted; shadow base published
+		warp_tally tn; tn.add(&s_n_cnt[it & 1u], go_on);
+		if (CLS == CLS_DIFFUSE && tid == 0) s_sh_base = pending_sh;
+		__syncthreads();
+		if (CLS == CLS_DIFFUSE && need_entry) {
+			uint32_t at = s_sh_base + tsh.ofs;
+			wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
+			wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
+			wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
+			if (sh_flags & SH_NEED2) {
+				wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
+				wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
 			}
 		}
-		uint32_t an = queue_push(cnt_next, go_on);
-		if (go_on) q_next[an] = slot;
+		if (tid == 0) {
+			uint32_t c = s_n_cnt[it & 1u];
+			pending_n = c ? atomicAdd(cnt_next, c) : 0u;
+			s_n_cnt[(it + 1u) & 1u] = 0;
+		}
+		p_go = go_on; p_ofs_n = tn.ofs; pslot = slot;
+		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u; it++;
+	}
+	if (it > 0) {
+		if (tid == 0) s_n_base[(it - 1u) & 1u] = pending_n;
+		__syncthreads();
+		if (p_go) q_next[s_n_base[(it - 1u) & 1u] + p_ofs_n] = pslot;
 	}
 }
 
@@ -321,44 +460,65 @@ __global__ void __launch_bounds__(256) k_shade(const __grid_constant__ scene_ref
 // The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
 // `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(256) k_connect(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
-	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	unsigned char* stage_base = (unsigned char*)plu_smem;
+	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
+	float4* st = (float4*)stage_base;   // [2][5][PLU_CTA]: p, w1, c1, w2, c2
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
 	const float4* thr_in = wb.thr[bounce & 1];
 	const float nl = (float)sc.n_lights;
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	uint32_t rays = 0;
-	const uint32_t lane = threadIdx.x & 31u;
-	for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
-		float4 p4 = wb.sh_p[j], w1 = wb.sh_w1[j];
-		uint32_t slot = __float_as_uint(p4.w), fl = __float_as_uint(w1.w);
-		int32_t li = (int32_t)(fl >> 8);
-		f3 Ld = mk3(0.f);
-		bool any = false;
-		ray r; r.e = mk3(p4);
-		if (fl & SH_NEED1) {
-			r.d = mk3(w1);
-			float t; int32_t prim;
-			rays++;
-			bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
-			// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
-			if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(wb.sh_c1[j]); any = true; }
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
+	auto gather = [&](uint32_t b, uint32_t jj) {
+		float4* row = st + (size_t)b * 5 * PLU_CTA + tid;
+		cp_async_16(row, wb.sh_p + jj); cp_async_16(row + PLU_CTA, wb.sh_w1 + jj); cp_async_16(row + 2 * PLU_CTA, wb.sh_c1 + jj);
+		cp_async_16(row + 3 * PLU_CTA, wb.sh_w2 + jj); cp_async_16(row + 4 * PLU_CTA, wb.sh_c2 + jj);
+	};
+	uint32_t j = blockIdx.x * PLU_CTA + tid, buf = 0;
+	if (j < n) gather(0, j);
+	cp_async_commit();
+	for (uint32_t j0 = j - lane; j0 < n; j0 += stride) {
+		const uint32_t jn = j + stride;
+		if (jn < n) gather(buf ^ 1u, jn);
+		cp_async_commit();
+		cp_async_wait<1>();
+		if (j < n) {
+			const float4* row = st + (size_t)buf * 5 * PLU_CTA + tid;
+			float4 p4 = row[0], w1 = row[PLU_CTA];
+			uint32_t slot = __float_as_uint(p4.w), fl = __float_as_uint(w1.w);
+			// path state is only needed after the casts: the loads travel meanwhile
+			float4 T4 = bounce == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : thr_in[slot];
+			float4 L4 = wb.rad[slot];
+			int32_t li = (int32_t)(fl >> 8);
+			f3 Ld = mk3(0.f);
+			bool any = false;
+			ray r; r.e = mk3(p4);
+			if (fl & SH_NEED1) {
+				r.d = mk3(w1);
+				float t; int32_t prim;
+				rays++;
+				bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
+				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
+			}
+			if (fl & SH_NEED2) {
+				r.d = mk3(row[3 * PLU_CTA]);
+				float t; int32_t prim;
+				rays++;
+				bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(row[4 * PLU_CTA]); any = true; }
+			}
+			f3 T = mk3(T4);
+			if (any || !finite3(T)) {
+				f3 L = mk3(L4);
+				L = L + T * (nl * Ld);
+				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+			}
 		}
-		if (fl & SH_NEED2) {
-			r.d = mk3(wb.sh_w2[j]);
-			float t; int32_t prim;
-			rays++;
-			bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
-			if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(wb.sh_c2[j]); any = true; }
-		}
-		f3 T = bounce == 0 ? mk3(1.f) : mk3(thr_in[slot]);
-		if (any || !finite3(T)) {
-			f3 L = mk3(wb.rad[slot]);
-			L = L + T * (nl * Ld);
-			wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
-		}
+		j = jn; buf ^= 1u;
 	}
 	unsigned long long a = rays, b = tc.nodes, c = tc.prims;
 	for (int o = 16; o > 0; o >>= 1) {

@@ -193,7 +193,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	CU(cudaFree(ctx->d_wave_mem)); ctx->d_wave_mem = nullptr; ctx->capacity = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = 10 * al(N * 16) + al(N * 8) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
+	size_t bytes = 10 * al(N * 16) + al(N * 8) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
 	CU(cudaMalloc(&ctx->d_wave_mem, bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave_mem;
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
@@ -206,7 +206,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	wb.hit = (int2*)take(N * 8);
 	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4);
 	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
-	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * 4 * sizeof(uint32_t));
+	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
 	if ((size_t)(p - (unsigned char*)ctx->d_wave_mem) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
 	ctx->capacity = slots;
@@ -216,23 +216,27 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 template <class K>
 static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 	int occ = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+	if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, PLU_CTA, smem) != cudaSuccess || occ < 1) occ = 1;
 	return ctx->sm_count * occ;
 }
 
-struct launch_cfg { bool smem, count; size_t smem_bytes; int g_gen, g_ext, g_shade[2], g_conn, g_acc; };
+// dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
+struct launch_cfg { bool smem, count; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_shade[2], g_conn, g_acc; };
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
-	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.smem_bytes = c.smem ? ctx->sc.blob_bytes : 0;
+	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count;
+	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
+	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
 	c.g_gen = grid_for(ctx, k_generate, 0);
 	c.g_acc = grid_for(ctx, k_accumulate, 0);
-#define PICK(var, K) \
-	var = c.smem ? (count ? grid_for(ctx, K<true, true>, c.smem_bytes) : grid_for(ctx, K<true, false>, c.smem_bytes)) \
-	             : (count ? grid_for(ctx, K<false, true>, 0) : grid_for(ctx, K<false, false>, 0))
-	PICK(c.g_ext, k_extend); PICK(c.g_conn, k_connect);
+#define PICK(var, K, SM) \
+	var = c.smem ? (count ? grid_for(ctx, K<true, true>, SM) : grid_for(ctx, K<true, false>, SM)) \
+	             : (count ? grid_for(ctx, K<false, true>, SM) : grid_for(ctx, K<false, false>, SM))
+	PICK(c.g_ext, k_extend, c.sm_ext); PICK(c.g_conn, k_connect, c.sm_conn);
 #undef PICK
-	c.g_shade[0] = c.smem ? grid_for(ctx, k_shade<true, CLS_DIFFUSE>, c.smem_bytes) : grid_for(ctx, k_shade<false, CLS_DIFFUSE>, 0);
-	c.g_shade[1] = c.smem ? grid_for(ctx, k_shade<true, CLS_SPECULAR>, c.smem_bytes) : grid_for(ctx, k_shade<false, CLS_SPECULAR>, 0);
+	c.g_shade[0] = c.smem ? grid_for(ctx, k_shade<true, CLS_DIFFUSE>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_DIFFUSE>, c.sm_shade);
+	c.g_shade[1] = c.smem ? grid_for(ctx, k_shade<true, CLS_SPECULAR>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_SPECULAR>, c.sm_shade);
 	return c;
 }
 
@@ -268,24 +272,24 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 	int launches = 1;
 	for (int b = 0; b < w.max_vertices; ++b) {
 		if (c.smem) {
-			if (c.count) k_extend<true, true><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
-			else k_extend<true, false><<<c.g_ext, 256, c.smem_bytes, st>>>(sc, wb, b, w.n_slots);
+			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
+			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], 256, c.smem_bytes, st>>>(sc, w, wb, b);
-			if (ctx->has_specular) { k_shade<true, CLS_SPECULAR><<<c.g_shade[1], 256, c.smem_bytes, st>>>(sc, w, wb, b); launches++; }
+			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
+			if (ctx->has_specular) { k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b); launches++; }
 			pf->mark(2, st);
-			if (c.count) k_connect<true, true><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
-			else k_connect<true, false><<<c.g_conn, 256, c.smem_bytes, st>>>(sc, wb, b);
+			if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
+			else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
 			pf->mark(3, st);
 		} else {
-			if (c.count) k_extend<false, true><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
-			else k_extend<false, false><<<c.g_ext, 256, 0, st>>>(sc, wb, b, w.n_slots);
+			if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
+			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], 256, 0, st>>>(sc, w, wb, b);
-			if (ctx->has_specular) { k_shade<false, CLS_SPECULAR><<<c.g_shade[1], 256, 0, st>>>(sc, w, wb, b); launches++; }
+			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
+			if (ctx->has_specular) { k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b); launches++; }
 			pf->mark(2, st);
-			if (c.count) k_connect<false, true><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
-			else k_connect<false, false><<<c.g_conn, 256, 0, st>>>(sc, wb, b);
+			if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
+			else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
 			pf->mark(3, st);
 		}
 		launches += 3;
