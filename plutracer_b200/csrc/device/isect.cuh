@@ -187,40 +187,64 @@ PLU_DEV bool trace_ref(const scene_ref& sc, const ray& r, float root_bound, floa
 	return best >= 0;
 }
 
+// aabb::hit / box::hit slab arithmetic once more, for the hot uniform walk: the 18 compare+select pairs
+// of glm::min/max become 6 FMNMX.NAN + 2 FMNMX3.NAN.  IEEE min/max agree with glm's `x<y?x:y` except
+// (1) when an operand is NaN and (2) in the sign of a zero result.  The .NaN forms make any NaN among
+// the six plane distances surface in BOTH results, so `tmin != tmin` is an exact hazard test; the
+// caller re-does the node with slabs_rrd() on a hazard (and on tmin == 0 where the value is returned
+// as a hit distance), so the outcome is the reference's bit for bit.
+PLU_DEV float fmin_nan(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+PLU_DEV float fmax_nan(float a, float b) { float r; asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+PLU_DEV float fmin3_nan(float a, float b, float c) { float r; asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV float fmax3_nan(float a, float b, float c) { float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV void slabs_fast(f3 mn, f3 mx, f3 e, f3 rrd, float& tmin, float& tmax) {
+	f3 t1 = (mn - e) * rrd;
+	f3 t2 = (mx - e) * rrd;
+	tmin = fmax3_nan(fmin_nan(t1.x, t2.x), fmin_nan(t1.y, t2.y), fmin_nan(t1.z, t2.z));
+	tmax = fmin3_nan(fmax_nan(t1.x, t2.x), fmax_nan(t1.y, t2.y), fmax_nan(t1.z, t2.z));
+}
+
 // scene->hit: the fast BVH when the scene has one (large scenes), else the reference's own tree.
 // Small scenes (all five named ones): the same walk as a WARP-UNIFORM loop over the pre-order node
 // array.  Every lane steps through every node index; a lane whose ray failed an ancestor's slab test
-// is merely predicated off until the loop reaches that ancestor's skip index.  Node, primitive and
-// tag reads are then one shared-memory broadcast per warp and the primitive-kind switch is uniform, so
-// there is no divergence left except the predicate itself (ncu r01: the per-lane walk ran at 18.4 of
-// 32 active threads per instruction).  Tested surfaces and the tie rule are unchanged.
-template <bool COUNT>
+// is merely predicated off until the loop reaches that ancestor's skip index.  Node reads are one
+// shared-memory broadcast per warp, so there is no divergence left except the predicate itself (ncu
+// r01: the per-lane walk ran at 18.4 of 32 active threads per instruction).  Interior nodes and box
+// leaves (a box leaf's node bounds ARE the box, bvh_build.cpp) share one branch-free slab test; a
+// sphere leaf carries (centre, radius) in its node; only triangles fetch primitive data.  Tested
+// surfaces and the tie rule are unchanged.
+template <bool COUNT, bool SMEM>
 PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bound, float& t_out, int32_t& prim_out, trace_counts* tc) {
 	const ref_node* nodes = sc.ref_nodes();
+	if (SMEM) __builtin_assume(__isShared(nodes));
 	const int32_t n = sc.n_ref_nodes;
 	const f3 rrd = 1.f / r.d;
 	const float bound = n == 1 ? root_bound : PLU_T_MAX;
 	float best_t = 0.f; int32_t best = -1;
 	int32_t skip_to = 0;
+#pragma unroll 2
 	for (int32_t i = 0; i < n; ++i) {
 		float4 lo = nodes[i].lo, hi = nodes[i].hi;
-		int32_t prim = __float_as_int(hi.w);
-		bool live = i >= skip_to;
-		if (prim >= 0) {   // uniform: leaf (lo.w carries the surface kind)
-			int32_t tag = __float_as_int(lo.w);
-			const float4* p = sc.prim(prim);
+		const int32_t prim = __float_as_int(hi.w), aux = __float_as_int(lo.w);   // aux: skip index | surface kind
+		const bool live = i >= skip_to;
+		const bool interior = prim < 0;
+		if (interior || aux == PLU_PRIM_BOX) {
+			float tmin, tmax; slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
+			if ((tmin != tmin) || (!interior && tmin == 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);   // hazard: exact glm order
+			if (interior) {
+				if (COUNT && live) tc->nodes++;
+				if (live && !(tmax >= tmin)) skip_to = aux;
+			} else {
+				if (COUNT && live) tc->prims++;
+				bool h = !(tmax < tmin || tmin < 0) && !(tmin > bound);
+				if (live && h && (best < 0 || !(best_t < tmin))) { best_t = tmin; best = prim; }
+			}
+		} else {
 			float t; bool h;
-			if (tag == PLU_PRIM_BOX) {
-				float tmin, tmax; slabs_rrd(mk3(p[0]), mk3(p[1]), r.e, rrd, tmin, tmax);
-				h = !(tmax < tmin || tmin < 0) && !(tmin > bound); t = tmin;
-			} else if (tag == PLU_PRIM_SPHERE) h = sphere_t(p[0], r, bound, t);
-			else h = triangle_t(p[0], p[1], p[2], r, bound, t);
+			if (aux == PLU_PRIM_SPHERE) h = sphere_t(make_float4(lo.x, lo.y, lo.z, hi.x), r, bound, t);
+			else { const float4* p = sc.prim(prim); h = triangle_t(p[0], p[1], p[2], r, bound, t); }
 			if (COUNT && live) tc->prims++;
 			if (live && h && (best < 0 || !(best_t < t))) { best_t = t; best = prim; }
-		} else {
-			float tmin, tmax; slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
-			if (COUNT && live) tc->nodes++;
-			if (live && !(tmax >= tmin)) skip_to = __float_as_int(lo.w);
 		}
 	}
 	t_out = best_t; prim_out = best;
@@ -294,10 +318,10 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 // the reference also feeds it NON-unit directions (its shading frames are not orthonormal, Q9), for
 // which the quadratic accepts rays that miss the sphere's bounds — no geometric BVH can reproduce
 // that, so such rays take the reference's own tree whenever the scene has spheres.
-template <bool COUNT>
+template <bool COUNT, bool SMEM>
 PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc) {
 	if (sc.fast_nodes != nullptr && (!sc.has_spheres || fabsf(dot(r.d, r.d) - 1.f) <= 1e-5f)) return trace_fast<COUNT>(sc, r, t, prim, tc);
-	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT>(sc, r, root_bound, t, prim, tc);
+	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT, SMEM>(sc, r, root_bound, t, prim, tc);
 	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);
 }
 

@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 			ray r; r.e = mk3(o); r.d = mk3(d);
 			int flags = __float_as_int(d.w);
 			float t; int32_t prim;
-			if (trace_scene<COUNT>(sc, r, o.w, t, prim, &tc)) {
+			if (trace_scene<COUNT, SMEM>(sc, r, o.w, t, prim, &tc)) {
 				int4 meta = sc.prim_meta(prim);   // kind, material, light, tie rank
 				int32_t mtag = sc.material(meta.y).tag;
 				if (mtag == PLU_MAT_EMISSION) {
@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 				r.d = mk3(w1);
 				float t; int32_t prim;
 				rays++;
-				bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
 				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
 				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
 			}
@@ -508,7 +508,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 				r.d = mk3(row[3 * PLU_CTA]);
 				float t; int32_t prim;
 				rays++;
-				bool hit = trace_scene<COUNT>(sc, r, PLU_T_MAX, t, prim, &tc);
+				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
 				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(row[4 * PLU_CTA]); any = true; }
 			}
 			f3 T = mk3(T4);
@@ -565,7 +565,7 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ scen
 			r.e = mk3(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2]); r.d = mk3(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2]);
 		}
 		float t; int32_t prim; trace_counts tc;
-		if (trace_scene<false>(sc, r, PLU_T_MAX, t, prim, &tc)) {
+		if (trace_scene<false, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc)) {
 			hit_rec hr; fill_record(sc, prim, sc.prim_meta(prim).x, r, t, false, hr);
 			id[i] = prim; t_out[i] = t; n3[3 * i] = hr.norm.x; n3[3 * i + 1] = hr.norm.y; n3[3 * i + 2] = hr.norm.z;
 		} else { id[i] = -1; t_out[i] = 0.f; n3[3 * i] = 0.f; n3[3 * i + 1] = 0.f; n3[3 * i + 2] = 0.f; }

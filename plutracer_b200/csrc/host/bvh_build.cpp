@@ -62,6 +62,12 @@ box3 emit_ref(const plu_scene_desc* d, const std::vector<int32_t>& dfs, size_t l
 		out[me].prim = -1;
 	}
 	for (int i = 0; i < 3; ++i) { out[me].lo[i] = b.mn[i]; out[me].hi[i] = b.mx[i]; }
+	// leaf bounds are never tested (bvh_tree.cpp:40-42), so a leaf node carries what its surface test reads:
+	// a box leaf's bounds already ARE the box (min, max); a sphere leaf holds (centre | radius)
+	if (out[me].prim >= 0 && d->prim_tag[out[me].prim] == PLU_PRIM_SPHERE) {
+		const float* f = d->prim_data + (size_t)out[me].prim * 12;
+		for (int i = 0; i < 3; ++i) { out[me].lo[i] = f[i]; out[me].hi[i] = f[3]; }
+	}
 	// interior: index of the next node outside this subtree; leaf (whose successor is always me + 1):
 	// the surface kind, so the walk needs no second lookup
 	out[me].skip = out[me].prim >= 0 ? d->prim_tag[out[me].prim] : (int32_t)out.size();
