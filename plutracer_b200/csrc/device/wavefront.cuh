@@ -115,7 +115,8 @@ template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_grou
 #define PLU_CTA 256
 // staging bytes per kernel (two stages of per-thread rows), added to the scene blob in dynamic shared memory
 #define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)
-#define PLU_STAGE_SHADE (2 * (3 * PLU_CTA * 16 + PLU_CTA * 8))
+#define PLU_STAGE_SHADE_IN (2 * (3 * PLU_CTA * 16 + PLU_CTA * 8))
+#define PLU_STAGE_SHADE (PLU_STAGE_SHADE_IN + 2 * 5 * PLU_CTA * 16)   // + two stages of shadow-entry payload
 #define PLU_STAGE_CONNECT (2 * 5 * PLU_CTA * 16)
 
 extern __shared__ uint4 plu_smem[];
@@ -264,7 +265,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
@@ -294,14 +295,27 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	if (j < n) { slot = q_in[j]; gather(0, slot); }
 	cp_async_commit();
 	if (j + stride < n) slot_next = q_in[j + stride];
-	// CTA-level push state: the shadow-queue batch is reserved and written within the iteration (two
-	// barriers apart, the continuation is sampled in between); the next-queue batch is completed in the
-	// following iteration
-	__shared__ uint32_t s_sh_cnt[2], s_n_cnt[2], s_sh_base, s_n_base[2];
-	if (tid < 2) { s_sh_cnt[tid] = 0; s_n_cnt[tid] = 0; }
+	// CTA-level push state.  Both queues of an iteration (shadow entries, next extend queue) are counted
+	// into shared memory, reserved by ONE thread after the barrier and written in the FOLLOWING iteration;
+	// the shadow payload waits in shared memory meanwhile (st_pay), not in registers.
+	float4* st_pay = (float4*)(stage_base + PLU_STAGE_SHADE_IN);   // [2][5][PLU_CTA]: p|slot, w1|flags, c1, w2, c2
+	__shared__ uint32_t s_sh_cnt[3], s_n_cnt[3];
+	__shared__ uint2 s_base[2];   // (next-queue base, shadow-queue base)
+	if (tid < 3) { s_sh_cnt[tid] = 0; s_n_cnt[tid] = 0; }
 	__syncthreads();
 	uint32_t pending_sh = 0, pending_n = 0;   // thread 0
-	uint32_t pslot = 0, p_ofs_n = 0, buf = 0, it = 0; bool p_go = false;
+	uint32_t pslot = 0, p_ofs_n = 0, p_ofs_sh = 0, buf = 0, it = 0, k3 = 0; bool p_go = false, p_need = false;
+	auto flush = [&](uint32_t prev) {   // entries of iteration `prev`
+		uint2 gb = s_base[prev & 1u];
+		if (p_go) q_next[gb.x + p_ofs_n] = pslot;
+		if (CLS == CLS_DIFFUSE && p_need) {
+			const float4* row = st_pay + (size_t)(prev & 1u) * 5 * PLU_CTA + tid;
+			uint32_t at = gb.y + p_ofs_sh;
+			float4 w1 = row[PLU_CTA];
+			wb.sh_p[at] = row[0]; wb.sh_w1[at] = w1; wb.sh_c1[at] = row[2 * PLU_CTA];
+			if (__float_as_uint(w1.w) & SH_NEED2) { wb.sh_w2[at] = row[3 * PLU_CTA]; wb.sh_c2[at] = row[4 * PLU_CTA]; }
+		}
+	};
 	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
 		const uint32_t jn = j + stride, jnn = jn + stride;
 		const bool has_next = jn < n;
@@ -402,57 +416,52 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 				L = L + T * (nl * mk3(0.f));
 				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 			}
-		}
-		// barrier 1: shadow batch counted; previous iteration's next-queue base published
-		warp_tally tsh; tsh.ofs = 0;
-		if (CLS == CLS_DIFFUSE) tsh.add(&s_sh_cnt[it & 1u], need_entry);
-		if (tid == 0 && it > 0) s_n_base[(it - 1u) & 1u] = pending_n;
-		__syncthreads();
-		if (it > 0 && p_go) q_next[s_n_base[(it - 1u) & 1u] + p_ofs_n] = pslot;
-		if (CLS == CLS_DIFFUSE && tid == 0) {   // the global atomic travels while the continuation is sampled
-			uint32_t c = s_sh_cnt[it & 1u];
-			pending_sh = c ? atomicAdd(cnt_shadow, c) : 0u;
-			s_sh_cnt[(it + 1u) & 1u] = 0;
-		}
-		// renderer.cpp:76-83: continuation
-		if (active && bounce < w.max_vertices - 1) {
-			uint32_t types = 0; float pdf; f3 wi;
-			f3 f = b.sampleF(rng, 1, nrm, wo, wi, pdf, BX_ALL, types);
-			if (!(dot(f, f) == 0.f || pdf == 0.f)) {
-				T = T * (f * fabsf(dot(wi, nrm)) / pdf);
-				int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
-				wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
-				wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
-				thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
-				go_on = true;
+			if (CLS == CLS_DIFFUSE && need_entry) {   // park the shadow entry in shared memory until its queue position is known
+				float4* row = st_pay + (size_t)(it & 1u) * 5 * PLU_CTA + tid;
+				row[0] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
+				row[PLU_CTA] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
+				row[2 * PLU_CTA] = make_float4(c1.x, c1.y, c1.z, 0.f);
+				if (sh_flags & SH_NEED2) {
+					row[3 * PLU_CTA] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
+					row[4 * PLU_CTA] = make_float4(c2.x, c2.y, c2.z, 0.f);
+				}
+			}
+			// renderer.cpp:76-83: continuation
+			if (bounce < w.max_vertices - 1) {
+				uint32_t types = 0; float pdf; f3 wi;
+				f3 f = b.sampleF(rng, 1, nrm, wo, wi, pdf, BX_ALL, types);
+				if (!(dot(f, f) == 0.f || pdf == 0.f)) {
+					T = T * (f * fabsf(dot(wi, nrm)) / pdf);
+					int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
+					wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
+					wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
+					thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
+					go_on = true;
+				}
 			}
 		}
-		// barrier 2: next-queue batch counted; shadow base published
-		warp_tally tn; tn.add(&s_n_cnt[it & 1u], go_on);
-		if (CLS == CLS_DIFFUSE && tid == 0) s_sh_base = pending_sh;
+		// count this iteration's batches; publish the bases of the previous one; ONE barrier
+		warp_tally tsh, tn; tsh.ofs = 0;
+		if (CLS == CLS_DIFFUSE) tsh.add(&s_sh_cnt[k3], need_entry);
+		tn.add(&s_n_cnt[k3], go_on);
+		if (tid == 0 && it > 0) s_base[(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
 		__syncthreads();
-		if (CLS == CLS_DIFFUSE && need_entry) {
-			uint32_t at = s_sh_base + tsh.ofs;
-			wb.sh_p[at] = make_float4(p.x, p.y, p.z, __uint_as_float(slot));
-			wb.sh_w1[at] = make_float4(wi1.x, wi1.y, wi1.z, __uint_as_float(sh_flags));
-			wb.sh_c1[at] = make_float4(c1.x, c1.y, c1.z, 0.f);
-			if (sh_flags & SH_NEED2) {
-				wb.sh_w2[at] = make_float4(wi2.x, wi2.y, wi2.z, 0.f);
-				wb.sh_c2[at] = make_float4(c2.x, c2.y, c2.z, 0.f);
-			}
+		if (it > 0) flush(it - 1u);
+		if (tid == 0) {   // the global atomics travel during the next iteration
+			uint32_t cn = s_n_cnt[k3], cs = CLS == CLS_DIFFUSE ? s_sh_cnt[k3] : 0u;
+			pending_n = cn ? atomicAdd(cnt_next, cn) : 0u;
+			pending_sh = cs ? atomicAdd(cnt_shadow, cs) : 0u;
+			uint32_t kz = k3 == 0 ? 2u : k3 - 1u;   // (it + 2) % 3
+			s_n_cnt[kz] = 0; s_sh_cnt[kz] = 0;
 		}
-		if (tid == 0) {
-			uint32_t c = s_n_cnt[it & 1u];
-			pending_n = c ? atomicAdd(cnt_next, c) : 0u;
-			s_n_cnt[(it + 1u) & 1u] = 0;
-		}
-		p_go = go_on; p_ofs_n = tn.ofs; pslot = slot;
-		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u; it++;
+		p_go = go_on; p_ofs_n = tn.ofs; p_need = need_entry; p_ofs_sh = tsh.ofs; pslot = slot;
+		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u;
+		it++; k3 = k3 == 2 ? 0u : k3 + 1u;
 	}
 	if (it > 0) {
-		if (tid == 0) s_n_base[(it - 1u) & 1u] = pending_n;
+		if (tid == 0) s_base[(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
 		__syncthreads();
-		if (p_go) q_next[s_n_base[(it - 1u) & 1u] + p_ofs_n] = pslot;
+		flush(it - 1u);
 	}
 }
 
