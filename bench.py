@@ -157,6 +157,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--spp-per-step", type=int, default=NSTRATA * NSTRATA)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strata-per-wave", type=int, default=0, help="paths in flight = W*H*this (0: library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)
@@ -182,7 +183,7 @@ def main():
     assert spp % world == 0 and 0 < spp <= NSTRATA * NSTRATA
     per_rank = spp // world
     # rank r takes strata r, r + world, ... of the first `spp` strata
-    params = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=rank, sample_stride=world, sample_count=per_rank)
+    params = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=rank, sample_stride=world, sample_count=per_rank, strata_per_wave=args.strata_per_wave)
     fb = torch.zeros(H, W, 3, dtype=torch.float32, device="cuda")
     flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device="cuda")
     stream = torch.cuda.current_stream()

@@ -40,6 +40,23 @@ PLU_DEV void slabs_rrd(f3 mn, f3 mx, f3 e, f3 rrd, float& tmin, float& tmax) {
 	tmax = x12.x; tmax = gmin(tmax, x12.y); tmax = gmin(tmax, x12.z);
 }
 
+// aabb::hit / box::hit slab arithmetic once more, for the hot uniform walk: the 18 compare+select pairs
+// of glm::min/max become 6 FMNMX.NAN + 2 FMNMX3.NAN.  IEEE min/max agree with glm's `x<y?x:y` except
+// (1) when an operand is NaN and (2) in the sign of a zero result.  The .NaN forms make any NaN among
+// the six plane distances surface in BOTH results, so `tmin != tmin` is an exact hazard test; the
+// caller re-does the node with slabs_rrd() on a hazard (and on tmin == 0 where the value is returned
+// as a hit distance), so the outcome is the reference's bit for bit.
+PLU_DEV float fmin_nan(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+PLU_DEV float fmax_nan(float a, float b) { float r; asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+PLU_DEV float fmin3_nan(float a, float b, float c) { float r; asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV float fmax3_nan(float a, float b, float c) { float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV void slabs_fast(f3 mn, f3 mx, f3 e, f3 rrd, float& tmin, float& tmax) {
+	f3 t1 = (mn - e) * rrd;
+	f3 t2 = (mx - e) * rrd;
+	tmin = fmax3_nan(fmin_nan(t1.x, t2.x), fmin_nan(t1.y, t2.y), fmin_nan(t1.z, t2.z));
+	tmax = fmin3_nan(fmax_nan(t1.x, t2.x), fmax_nan(t1.y, t2.y), fmax_nan(t1.z, t2.z));
+}
+
 // t-only versions of surface::hit(r, hr) with hr->t == bound on entry.
 PLU_DEV bool sphere_t(float4 cr, const ray& r, float bound, float& t) {   // sphere.cpp:17-26
 	f3 v = r.e - mk3(cr);
@@ -55,7 +72,9 @@ PLU_DEV bool sphere_t(float4 cr, const ray& r, float bound, float& t) {   // sph
 	return false;
 }
 PLU_DEV bool box_t(float4 mn, float4 mx, const ray& r, float bound, float& t) {   // box.cpp:8-27
-	float tmin, tmax; slabs(mk3(mn), mk3(mx), r, tmin, tmax);
+	const f3 rrd = 1.f / r.d;
+	float tmin, tmax; slabs_fast(mk3(mn), mk3(mx), r.e, rrd, tmin, tmax);
+	if ((tmin != tmin) || tmin == 0.f) slabs_rrd(mk3(mn), mk3(mx), r.e, rrd, tmin, tmax);   // hazard: exact glm order
 	if (tmax < tmin || tmin < 0) return false;
 	if (tmin > bound) return false;
 	t = tmin; return true;
@@ -185,23 +204,6 @@ PLU_DEV bool trace_ref(const scene_ref& sc, const ray& r, float root_bound, floa
 	}
 	t_out = best_t; prim_out = best;
 	return best >= 0;
-}
-
-// aabb::hit / box::hit slab arithmetic once more, for the hot uniform walk: the 18 compare+select pairs
-// of glm::min/max become 6 FMNMX.NAN + 2 FMNMX3.NAN.  IEEE min/max agree with glm's `x<y?x:y` except
-// (1) when an operand is NaN and (2) in the sign of a zero result.  The .NaN forms make any NaN among
-// the six plane distances surface in BOTH results, so `tmin != tmin` is an exact hazard test; the
-// caller re-does the node with slabs_rrd() on a hazard (and on tmin == 0 where the value is returned
-// as a hit distance), so the outcome is the reference's bit for bit.
-PLU_DEV float fmin_nan(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
-PLU_DEV float fmax_nan(float a, float b) { float r; asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
-PLU_DEV float fmin3_nan(float a, float b, float c) { float r; asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
-PLU_DEV float fmax3_nan(float a, float b, float c) { float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
-PLU_DEV void slabs_fast(f3 mn, f3 mx, f3 e, f3 rrd, float& tmin, float& tmax) {
-	f3 t1 = (mn - e) * rrd;
-	f3 t2 = (mx - e) * rrd;
-	tmin = fmax3_nan(fmin_nan(t1.x, t2.x), fmin_nan(t1.y, t2.y), fmin_nan(t1.z, t2.z));
-	tmax = fmin3_nan(fmax_nan(t1.x, t2.x), fmax_nan(t1.y, t2.y), fmax_nan(t1.z, t2.z));
 }
 
 // scene->hit: the fast BVH when the scene has one (large scenes), else the reference's own tree.

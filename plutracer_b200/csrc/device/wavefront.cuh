@@ -21,10 +21,15 @@
 namespace plud {
 
 struct wave_buffers {
-	float4* ray_o;        // e.xyz, hit_record::t the next scene->hit starts from (only read by a leaf root)
-	float4* ray_d;        // d.xyz, flags
-	int2* hit;            // (t bits, surface id)
-	float4* thr[2];       // path_throughput, ping-pong by bounce parity
+	// Path state: one 64-byte record per slot = one DRAM access atom.  Queues hold slot ids, so state is
+	// GATHERED by index; with one array per field every 16-byte gather dragged a 64-byte atom from HBM
+	// (ncu r01e: k_shade read 340 B per vertex for 60 B of payload).
+	//   rec[4*slot+0] = (ray origin, hit_record::t the next scene->hit starts from)
+	//   rec[4*slot+1] = (ray direction, flags)
+	//   rec[4*slot+2] = (path_throughput for even vertices, t of the pending hit)
+	//   rec[4*slot+3] = (path_throughput for odd vertices, surface id of the pending hit)
+	// path_throughput ping-pongs by vertex parity: k_connect of vertex v still needs T before the vertex.
+	float4* rec;
 	float4* rad;          // L
 	uint32_t* queue[2];   // extend queues, ping-pong
 	uint32_t* q_hit[2];   // paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR)
@@ -115,7 +120,7 @@ template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_grou
 #define PLU_CTA 256
 // staging bytes per kernel (two stages of per-thread rows), added to the scene blob in dynamic shared memory
 #define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)
-#define PLU_STAGE_SHADE_IN (2 * (3 * PLU_CTA * 16 + PLU_CTA * 8))
+#define PLU_STAGE_SHADE_IN (2 * 4 * PLU_CTA * 16)
 #define PLU_STAGE_SHADE (PLU_STAGE_SHADE_IN + 2 * 5 * PLU_CTA * 16)   // + two stages of shadow-entry payload
 #define PLU_STAGE_CONNECT (2 * 5 * PLU_CTA * 16)
 
@@ -124,7 +129,7 @@ extern __shared__ uint4 plu_smem[];
 // ---- k_generate -----------------------------------------------------------------------------------------------
 // stratified_sampler::generate_samples for one sample (sampler.h:58-69): stratum (s % n, s / n),
 // px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.
-__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb) {
+__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb) {
 	for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < w.n_slots; slot += gridDim.x * blockDim.x) {
 		philox_key key; int32_t px_x, px_y, s;
 		slot_to_path(w, slot, key, px_x, px_y, s);
@@ -135,8 +140,8 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_
 		f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);
 		f2 lens = mk2((sx + u01(o.z) * 0.999f) * dp, (sy + u01(o.w) * 0.999f) * dp);
 		ray r = generate_ray(sc_in.cam, px, lens, w.use_lens != 0);
-		wb.ray_o[slot] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
-		wb.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
+		wb.rec[4 * (size_t)slot] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
+		wb.rec[4 * (size_t)slot + 1] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
 		wb.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
 }
@@ -146,8 +151,9 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_
 // into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
 // the queue entry of iteration i+2; queue pushes started in iteration i are completed in iteration i+1.
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce, uint32_t n_identity) {
+__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce, uint32_t n_identity) {
 	scene_ref sc = sc_in;
+	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
@@ -166,7 +172,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 	uint32_t slot = 0, slot_next = 0;
 	if (j < n) {
 		slot = ident ? j : q[j];
-		cp_async_16(st_o + tid, wb.ray_o + slot); cp_async_16(st_d + tid, wb.ray_d + slot);
+		cp_async_16(st_o + tid, recs + 4 * (size_t)slot); cp_async_16(st_d + tid, recs + 4 * (size_t)slot + 1);
 	}
 	cp_async_commit();
 	if (j + stride < n) slot_next = ident ? j + stride : q[j + stride];
@@ -184,8 +190,8 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 		const uint32_t jn = j + stride, jnn = jn + stride;
 		const bool has_next = jn < n;
 		if (has_next) {
-			cp_async_16(st_o + (buf ^ 1u) * PLU_CTA + tid, wb.ray_o + slot_next);
-			cp_async_16(st_d + (buf ^ 1u) * PLU_CTA + tid, wb.ray_d + slot_next);
+			cp_async_16(st_o + (buf ^ 1u) * PLU_CTA + tid, recs + 4 * (size_t)slot_next);
+			cp_async_16(st_d + (buf ^ 1u) * PLU_CTA + tid, recs + 4 * (size_t)slot_next + 1);
 		}
 		cp_async_commit();
 		uint32_t slot_nn = 0;
@@ -205,7 +211,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 					// its empty bsdf gives NEE = 0 and sampleF pdf = 0, i.e. the path ends here (renderer.cpp:78)
 					bool le = bounce == 0 || (flags & FLAG_SPEC);
 					if (le || (flags & FLAG_NONFINITE)) {
-						f3 T = bounce == 0 ? mk3(1.f) : mk3(wb.thr[bounce & 1][slot]);
+						f3 T = bounce == 0 ? mk3(1.f) : mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]);
 						f3 L = mk3(wb.rad[slot]);
 						if (le) {
 							hit_rec hr; fill_record(sc, prim, meta.x, r, t, false, hr);
@@ -215,14 +221,15 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 						wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 					}
 				} else {
-					wb.hit[slot] = make_int2(__float_as_int(t), prim);
+					float* rw = (float*)(recs + 4 * (size_t)slot);   // the .w words of quarters 2 and 3
+					rw[11] = t; rw[15] = __int_as_float(prim);
 					to_diffuse = mtag == PLU_MAT_DIFFUSE; to_specular = !to_diffuse;
 				}
 			} else {
 				// renderer.cpp:87-90: after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
 				// a no-op unless T is not finite
 				if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
-					f3 T = mk3(wb.thr[bounce & 1][slot]); f3 L = mk3(wb.rad[slot]);
+					f3 T = mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]); f3 L = mk3(wb.rad[slot]);
 					for (int32_t i = 0; i < sc.n_lights; ++i) L = L + T * mk3(0.f);
 					wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 				}
@@ -265,30 +272,26 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(PLU_CTA) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
+	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
-	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
-	float4* st_d = st_o + 2 * PLU_CTA;
-	float4* st_T = st_d + 2 * PLU_CTA;
-	int2* st_h = (int2*)(st_T + 2 * PLU_CTA);
+	float4* st_rec = (float4*)stage_base;          // [2][4][PLU_CTA]: the four quarters of the path record
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
 	const uint32_t* q_in = wb.q_hit[CLS];
 	uint32_t* cnt_shadow = wb.counters + bounce * CNT_STRIDE + CNT_SHADOW;
 	uint32_t* cnt_next = wb.counters + (bounce + 1) * CNT_STRIDE + CNT_EXTEND;
 	uint32_t* q_next = wb.queue[(bounce + 1) & 1];
-	const float4* thr_in = wb.thr[bounce & 1];
-	float4* thr_out = wb.thr[(bounce + 1) & 1];
-	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
+	const uint32_t tid = threadIdx.x, stride = gridDim.x * PLU_CTA;
 	const float nl = (float)sc.n_lights;
-	const bool first = bounce == 0;
+	const uint32_t q_T_in = 2u + ((uint32_t)bounce & 1u), q_T_out = 2u + (((uint32_t)bounce + 1u) & 1u);
 
-	auto gather = [&](uint32_t b, uint32_t sl) {
-		cp_async_16(st_o + b * PLU_CTA + tid, wb.ray_o + sl); cp_async_16(st_d + b * PLU_CTA + tid, wb.ray_d + sl);
-		cp_async_8(st_h + b * PLU_CTA + tid, wb.hit + sl);
-		if (!first) cp_async_16(st_T + b * PLU_CTA + tid, thr_in + sl);
+	auto gather = [&](uint32_t b, uint32_t sl) {   // the whole 64-byte record of the slot
+		float4* dst = st_rec + (size_t)b * 4 * PLU_CTA + tid;
+		const float4* src = recs + 4 * (size_t)sl;
+		cp_async_16(dst, src); cp_async_16(dst + PLU_CTA, src + 1); cp_async_16(dst + 2 * PLU_CTA, src + 2); cp_async_16(dst + 3 * PLU_CTA, src + 3);
 	};
 	uint32_t j = blockIdx.x * PLU_CTA + tid;
 	uint32_t slot = 0, slot_next = 0;
@@ -328,19 +331,21 @@ __global__ void __launch_bounds__(PLU_CTA) k_shade(const __grid_constant__ scene
 		uint32_t sh_flags = 0;
 		f3 p = mk3(0.f), wi1 = mk3(0.f), c1 = mk3(0.f), wi2 = mk3(0.f), c2 = mk3(0.f);
 		f3 T = mk3(1.f), nrm = mk3(0.f), wo = mk3(0.f);
-		float t = 0.f; int flags = 0;
+		float t = 0.f, hit_w_keep = 0.f; int flags = 0;
 		bsdf b; vertex_rng rng;
 		b.tag = PLU_MAT_DIFFUSE;
 		if (active) {
-			float4 o4 = st_o[buf * PLU_CTA + tid], d4 = st_d[buf * PLU_CTA + tid];
-			int2 h = st_h[buf * PLU_CTA + tid];
+			const float4* row = st_rec + (size_t)buf * 4 * PLU_CTA + tid;
+			float4 o4 = row[0], d4 = row[PLU_CTA], q2 = row[2 * PLU_CTA], q3 = row[3 * PLU_CTA];
+			int2 h = make_int2(__float_as_int(q2.w), __float_as_int(q3.w));
+			hit_w_keep = q_T_out == 2u ? q2.w : q3.w;   // the .w of the quarter that receives the new throughput
 			ray r; r.e = mk3(o4); r.d = mk3(d4);
 			flags = __float_as_int(d4.w);
 			t = __int_as_float(h.x); int32_t prim = h.y;
 			int4 meta = sc.prim_meta(prim);   // kind, material, light (-1 here: emissive hits end in k_extend), tie rank
 			const plu_material_desc& m = sc.material(meta.y);
 			hit_rec hr; fill_record(sc, prim, meta.x, r, t, m.texture >= 0, hr);
-			if (!first) T = mk3(st_T[buf * PLU_CTA + tid]);
+			if (bounce != 0) T = q_T_in == 2u ? mk3(q2) : mk3(q3);
 			philox_key key; int32_t px_x, px_y, s;
 			slot_to_path(w, slot, key, px_x, px_y, s);
 			if (CLS == CLS_DIFFUSE) rng.begin(key, bounce);
@@ -433,9 +438,10 @@ __global__ void __launch_bounds__(PLU_CTA) k_shade(const __grid_constant__ scene
 				if (!(dot(f, f) == 0.f || pdf == 0.f)) {
 					T = T * (f * fabsf(dot(wi, nrm)) / pdf);
 					int nf = ((types & BX_SPECULAR) ? FLAG_SPEC : 0) | (finite3(T) ? 0 : FLAG_NONFINITE);
-					wb.ray_o[slot] = make_float4(p.x, p.y, p.z, t);
-					wb.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
-					thr_out[slot] = make_float4(T.x, T.y, T.z, 0.f);
+					float4* rec = recs + 4 * (size_t)slot;
+					rec[0] = make_float4(p.x, p.y, p.z, t);
+					rec[1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
+					rec[q_T_out] = make_float4(T.x, T.y, T.z, hit_w_keep);
 					go_on = true;
 				}
 			}
@@ -469,14 +475,14 @@ __global__ void __launch_bounds__(PLU_CTA) k_shade(const __grid_constant__ scene
 // The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
 // `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
+	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st = (float4*)stage_base;   // [2][5][PLU_CTA]: p, w1, c1, w2, c2
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
-	const float4* thr_in = wb.thr[bounce & 1];
 	const float nl = (float)sc.n_lights;
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	uint32_t rays = 0;
@@ -499,7 +505,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 			float4 p4 = row[0], w1 = row[PLU_CTA];
 			uint32_t slot = __float_as_uint(p4.w), fl = __float_as_uint(w1.w);
 			// path state is only needed after the casts: the loads travel meanwhile
-			float4 T4 = bounce == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : thr_in[slot];
+			float4 T4 = bounce == 0 ? make_float4(1.f, 1.f, 1.f, 0.f) : recs[4 * (size_t)slot + 2 + (bounce & 1)];
 			float4 L4 = wb.rad[slot];
 			int32_t li = (int32_t)(fl >> 8);
 			f3 Ld = mk3(0.f);
@@ -543,7 +549,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 // ---- k_accumulate ---------------------------------------------------------------------------------------------
 // target->pixel(floor(px)) += ray_color * smp_wgt, samples in ascending order (renderer.cpp:132).
 // The overflow-column strip (pixel index >= W*H, sampler.h:74-78) lands in pixel (0, row+1).
-__global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave_desc w, wave_buffers wb, float* fb, float smp_wgt) {
+__global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb, float* fb, float smp_wgt) {
 	for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < (uint32_t)w.npix; q += gridDim.x * blockDim.x) {
 		int32_t pix = w.pix0 + (int32_t)q, wh = w.width * w.height;
 		int32_t dst = pix < wh ? pix : (pix - wh + 1) * w.width;

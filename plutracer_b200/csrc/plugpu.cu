@@ -193,17 +193,15 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	CU(cudaFree(ctx->d_wave_mem)); ctx->d_wave_mem = nullptr; ctx->capacity = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = 10 * al(N * 16) + al(N * 8) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
+	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
 	CU(cudaMalloc(&ctx->d_wave_mem, bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave_mem;
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
 	wave_buffers& wb = ctx->wb;
 	// 16-byte rows first so every array is 256-byte aligned
-	wb.ray_o = (float4*)take(N * 16); wb.ray_d = (float4*)take(N * 16);
-	wb.thr[0] = (float4*)take(N * 16); wb.thr[1] = (float4*)take(N * 16); wb.rad = (float4*)take(N * 16);
+	wb.rec = (float4*)take(N * 64); wb.rad = (float4*)take(N * 16);
 	wb.sh_p = (float4*)take(N * 16); wb.sh_w1 = (float4*)take(N * 16); wb.sh_c1 = (float4*)take(N * 16);
 	wb.sh_w2 = (float4*)take(N * 16); wb.sh_c2 = (float4*)take(N * 16);
-	wb.hit = (int2*)take(N * 8);
 	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4);
 	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
