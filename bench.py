@@ -87,6 +87,17 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(kernel):
+    """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed `ncu --set full` capture
+    (profiles/traffic.json, written by tools/ncu_traffic.py from the .ncu-rep of this same command)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f)[kernel]
+        return float(e["dram_bytes_per_launch"]), e.get("source", "profiles/traffic.json")
+    except Exception:
+        return None, None
+
+
 # ---- the reference's own CPU renderer (oracle/_ref/plu_ref = unmodified reference sources) -----------------
 def run_reference_cpu(smp, timeout=900):
     """renderer::render of the compiled reference on the host cores; returns (samples/s, info)."""
@@ -165,7 +176,7 @@ def main():
     import numpy as np
     import torch
     import torch.distributed as dist
-    from plutracer_b200 import GpuContext, Scene, _ffi, renderer, stratified_sampler, texture2d
+    from plutracer_b200 import GpuContext, Scene, _ffi, renderer, shard_plan, sharded_renderer, stratified_sampler, texture2d
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if not torch.cuda.is_available():
@@ -180,10 +191,10 @@ def main():
     ctx = GpuContext(local)
     ctx.upload(scene)
     spp = args.spp_per_step
-    assert spp % world == 0 and 0 < spp <= NSTRATA * NSTRATA
-    per_rank = spp // world
-    # rank r takes strata r, r + world, ... of the first `spp` strata
-    params = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=rank, sample_stride=world, sample_count=per_rank, strata_per_wave=args.strata_per_wave)
+    assert 0 < spp <= NSTRATA * NSTRATA and spp >= world
+    # rank r takes strata r, r + world, ... of the first `spp` strata (plutracer_b200/shard.py)
+    s_begin, s_stride, s_count = shard_plan(NSTRATA, world, rank, spp)
+    params = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=s_begin, sample_stride=s_stride, sample_count=s_count, strata_per_wave=args.strata_per_wave)
     fb = torch.zeros(H, W, 3, dtype=torch.float32, device="cuda")
     flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device="cuda")
     stream = torch.cuda.current_stream()
@@ -225,36 +236,49 @@ def main():
     value = samples_per_step / (ms_per_step * 1e-3) / 1e6
     rays_per_sample = (st.rays_extend + st.rays_shadow) / max(st.samples, 1)
 
+    # ---- e2e: the reference-facing call with HOST buffers (every rank takes part when N > 1) ------------------
+    tx = texture2d((W, H))
+    fb_bytes = W * H * 3 * 4
+    n_e2e = max(1, min(args.steps, 2))
+    if world == 1:
+        r = renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, seed=SEED)
+
+        def e2e_step():   # scene upload + framebuffer H2D (`+=`) + render + framebuffer D2H, all inside plu_gpu_render
+            tx.pixels.fill(0)
+            if spp == NSTRATA * NSTRATA:
+                return r.render(tx)
+            p = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=0, sample_stride=1, sample_count=spp)
+            r.ctx.upload(scene)
+            return r.ctx.render(p, tx.pixels)
+        h2d, d2h = fb_bytes + 1024, fb_bytes
+    else:
+        r = sharded_renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, rank=rank, world=world, seed=SEED)
+
+        def e2e_step():   # rank 0: pinned host pixels -> device; all: render own strata; NCCL reduce; rank 0: device -> host
+            tx.pixels.fill(0)
+            return r.render(tx, spp=spp)
+        h2d, d2h = fb_bytes, fb_bytes
+    e2e_step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    dt = (time.perf_counter() - t0) / n_e2e
+    te = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    dt = float(te.item())
+    e2e = {"value": samples_per_step / dt / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "ms_per_step": dt * 1e3, "timing": "host wall clock around the call, max over ranks"}
+    r.ctx.close()
+
     line = None
     if rank == 0:
-        # ---- e2e: the reference-facing call with host buffers -----------------------------------------------
-        tx = texture2d((W, H))
-        r = renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, seed=SEED)
-        e2e = None
-        if world == 1:
-            e_params_count = spp
-            r.ctx.upload(scene)
-
-            def e2e_step():
-                tx.pixels.fill(0)
-                if spp == NSTRATA * NSTRATA:
-                    return r.render(tx)
-                p = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=0, sample_stride=1, sample_count=spp)
-                r.ctx.upload(scene)
-                return r.ctx.render(p, tx.pixels)
-            e2e_step()
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            n_e2e = max(1, min(args.steps, 2))
-            for _ in range(n_e2e):
-                e2e_step()
-            torch.cuda.synchronize()
-            dt = (time.perf_counter() - t0) / n_e2e
-            fb_bytes = W * H * 3 * 4
-            e2e = {"value": W * H * e_params_count / dt / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": fb_bytes + 1024,
-                   "d2h_bytes_per_step": fb_bytes, "ms_per_step": dt * 1e3}
-        r.ctx.close()
-
         # ---- roofline of the dominant kernel, measured live (profiled pass, CUDA events between launches) ----
         peak, peak_src = measured_peak()
         pp = GpuContext.params(W, H, NSTRATA, seed=SEED, flags=_ffi.RENDER_PROFILE, sample_begin=0, sample_stride=1, sample_count=min(spp, 256))
@@ -276,12 +300,14 @@ def main():
         n_dom = int(ps.waves) * 8 * (2 if dom == "k_shade" else 1)   # launches of that kernel class in the profiled pass
         achieved = alg[dom] / (ms[dom] * 1e-3) / 1e9 if ms[dom] > 0 else 0.0
         bytes_per_sample = (alg["k_extend"] + alg["k_shade"] + alg["k_connect"]) / max(ps.samples, 1) + 12.0
-        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        traffic, traffic_src = measured_traffic(dom)
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                    "traffic_source": traffic_src, "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
                     "peak_source": peak_src, "launches_profiled": int(n_dom), "avg_launch_ms": ms[dom] / max(n_dom, 1),
                     "ms_by_kernel": {"k_generate": ps.ms_generate, **ms, "k_accumulate": ps.ms_accumulate},
                     "algorithmic_bytes_per_sample": bytes_per_sample, "b_bvh_per_ray": b_bvh,
-                    "whole_path_achieved_gbs": bytes_per_sample * value * 1e6 / 1e9,
-                    "whole_path_frac": bytes_per_sample * value * 1e6 / 1e9 / peak}
+                    "whole_path_achieved_gbs": bytes_per_sample * value / world * 1e6 / 1e9,   # per GPU
+                    "whole_path_frac": bytes_per_sample * value / world * 1e6 / 1e9 / peak}
         cpu = None if (args.no_cpu_baseline or world > 1) else cpu_arm(4)
         line = {"metric": "Msamples/s on cornell-box.urn at 1024x1024, 4096 spp", "value": value, "unit": "Msamples/s", "n_gpus": world,
                 "steps": args.steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
@@ -292,8 +318,7 @@ def main():
                            "seed": SEED},
                 "mrays_per_s": value * rays_per_sample, "rays_per_sample": rays_per_sample,
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
-        if e2e is not None:
-            line["e2e"] = e2e
+        line["e2e"] = e2e
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line))
