@@ -266,14 +266,18 @@ PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bou
 template <bool COUNT>
 PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc) {
 	const fast_node* nodes = sc.fast_nodes;
+	const float4* leaves = sc.fast_leaf;   // 3 x float4 per leaf slot, in leaf order (plugpu.cu: upload)
 	const float ix = 1.f / r.d.x, iy = 1.f / r.d.y, iz = 1.f / r.d.z;
 	float best_t = 3.0e38f; int32_t best = -1, best_rank = -1;
-	int32_t stack[128]; int sp = 0;   // host/bvh_build.cpp bounds the tree depth to 60
-	int32_t cur = 0;   // node index >= 0, or leaf ~first
-	int32_t cur_count = 0;
-	if (sc.n_fast_nodes == 0) { t_out = 0.f; prim_out = -1; return false; }
-	for (;;) {
-		if (cur >= 0) {
+	// child reference: >= 0 inner node index; < 0 leaf ~((first_slot << 3) | count); DONE = stack exhausted
+	const int32_t DONE = (int32_t)0x80000000;
+	int32_t stack[64]; int sp = 0;   // host/bvh_build.cpp bounds the tree depth to 60
+	int32_t cur = sc.n_fast_nodes > 0 ? 0 : DONE;
+	// "while-while" walk: every lane first descends to its next leaf, then the warp tests leaves together;
+	// with one if/else per step (r01f: 8.6 of 32 threads active per instruction) node and leaf work of
+	// different lanes alternated serially
+	while (cur != DONE) {
+		while (cur >= 0) {
 			const fast_node* nd = nodes + cur;
 			float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c); int4 d = __ldg(&nd->d);
 			if (COUNT) tc->nodes++;
@@ -290,27 +294,26 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 			bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull);
 			if (h0 && h1) {
 				bool first1 = n1 < n0;   // nearer child first; the other goes on the stack
-				int32_t far_c = first1 ? d.x : d.y, far_n = first1 ? d.z : d.w;
-				stack[sp++] = far_c; stack[sp++] = far_n;
-				cur = first1 ? d.y : d.x; cur_count = first1 ? d.w : d.z;
-				continue;
-			}
-			if (h0) { cur = d.x; cur_count = d.z; continue; }
-			if (h1) { cur = d.y; cur_count = d.w; continue; }
-		} else {
-			int32_t first = ~cur;
-			for (int32_t k = 0; k < cur_count; ++k) {
-				int32_t prim = __ldg(sc.fast_prim_index + first + k);
-				int4 meta = sc.prim_meta(prim);
-				float t;
-				if (COUNT) tc->prims++;
-				if (prim_t(sc, prim, meta.x, r, PLU_T_MAX, t)) {
-					if (best < 0 || t < best_t || (t == best_t && meta.w > best_rank)) { best_t = t; best = prim; best_rank = meta.w; }
-				}
-			}
+				stack[sp++] = first1 ? d.x : d.y;
+				cur = first1 ? d.y : d.x;
+			} else if (h0) cur = d.x;
+			else if (h1) cur = d.y;
+			else cur = sp > 0 ? stack[--sp] : DONE;
 		}
-		if (sp == 0) break;
-		cur_count = stack[--sp]; cur = stack[--sp];
+		if (cur == DONE) break;
+		const int32_t first = (~cur) >> 3, count = (~cur) & 7;
+		for (int32_t k = 0; k < count; ++k) {
+			const float4* rec = leaves + 3 * (size_t)(first + k);
+			float4 a = __ldg(rec), b = __ldg(rec + 1);
+			const int32_t kr = __float_as_int(b.w), kind = (int32_t)((uint32_t)kr >> 30), rank = kr & 0x3fffffff;
+			float t; bool h; int32_t id;
+			if (COUNT) tc->prims++;
+			if (kind == PLU_PRIM_BOX) { id = __float_as_int(a.w); h = box_t(a, b, r, PLU_T_MAX, t); }
+			else if (kind == PLU_PRIM_SPHERE) { id = __float_as_int(b.x); h = sphere_t(a, r, PLU_T_MAX, t); }
+			else { id = __float_as_int(a.w); h = triangle_t(a, b, __ldg(rec + 2), r, PLU_T_MAX, t); }
+			if (h && (best < 0 || t < best_t || (t == best_t && rank > best_rank))) { best_t = t; best = id; best_rank = rank; }
+		}
+		cur = sp > 0 ? stack[--sp] : DONE;
 	}
 	t_out = best_t; prim_out = best;
 	return best >= 0;

@@ -20,7 +20,12 @@ struct ref_node { float4 lo, hi; };
 
 // Tight two-child node of the fast BVH (host/bvh_build.cpp), 64 B = four 128-bit loads:
 //   a = (c0.min.xyz, c0.max.x)  b = (c0.max.yz, c1.min.xy)  c = (c1.min.z, c1.max.xyz)
-//   d = (child0, child1, -, -) as int: >= 0 inner node index, < 0 leaf: ~first_prim_slot, count in .z/.w
+//   d = (child0, child1, -, -) as int: >= 0 inner node index, < 0 leaf: ~((first_leaf_slot << 3) | count)
+// Leaf slots hold the surfaces themselves in leaf order (fast_leaf, 3 x float4 each), so a leaf test is one
+// dependent load level instead of index -> meta -> data:
+//   box      a = (min | surface id)      b = (max | kind<<30 | tie rank)
+//   sphere   a = (centre | radius)       b = (surface id, -, - | kind<<30 | tie rank)
+//   triangle a = (v0 | surface id)       b = (v1 | kind<<30 | tie rank)       c = (v2 | -)
 struct fast_node { float4 a, b, c; int4 d; };
 
 struct scene_ref {
@@ -34,6 +39,7 @@ struct scene_ref {
 	const float* texels;            // image textures, rgb float
 	const fast_node* fast_nodes;    // null: traverse the reference tree
 	const int32_t* fast_prim_index; // leaf slots -> prim ids
+	const float4* fast_leaf;        // leaf slots -> surface records (see fast_node)
 	int32_t n_fast_nodes;
 	int32_t has_spheres;
 	plu_camera_desc cam;

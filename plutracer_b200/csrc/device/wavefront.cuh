@@ -176,13 +176,19 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 	}
 	cp_async_commit();
 	if (j + stride < n) slot_next = ident ? j + stride : q[j + stride];
-	// CTA-level push state (see warp_tally): counts [3] rotate so that thread 0 can clear one while the
-	// warps already add to the next; s_base is double-buffered for the same reason
-	__shared__ uint32_t s_cnt[3][2];
-	__shared__ uint2 s_base[2];
-	if (tid < 6) (&s_cnt[0][0])[tid] = 0;
+	// Push state of one GROUP (see warp_tally): the whole CTA when the scene is staged in shared memory (uniform
+	// walk: every warp takes the same time, one barrier per iteration is free), a single warp otherwise
+	// (large scenes: r01f had 34 % of k_extend's stall samples on the CTA barrier, rays of different length).
+	// counts [3] rotate so that the leader can clear one while the warps already add to the next; s_base
+	// is double-buffered for the same reason.
+	constexpr bool WARP_SCOPE = !SMEM;
+	const uint32_t grp = WARP_SCOPE ? (tid >> 5) : 0u;
+	const bool leader = WARP_SCOPE ? lane == 0 : tid == 0;
+	__shared__ uint32_t s_cnt[PLU_CTA / 32][3][2];
+	__shared__ uint2 s_base[PLU_CTA / 32][2];
+	if (tid < (PLU_CTA / 32) * 6) (&s_cnt[0][0][0])[tid] = 0;
 	__syncthreads();
-	unsigned long long pending = 0;   // thread 0: result of the CTA's global atomic of the previous iteration
+	unsigned long long pending = 0;   // leader: result of the group's global atomic of the previous iteration
 	uint32_t pslot = 0, p_ofs_d = 0, p_ofs_s = 0; bool p_d = false, p_s = false;
 	uint32_t buf = 0, it = 0, k3 = 0;
 	unsigned long long* cnt_pair = (unsigned long long*)cnt_diffuse;   // (diffuse, specular) = (low, high)
@@ -235,28 +241,28 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 				}
 			}
 		}
-		warp_tally td, ts; td.add(&s_cnt[k3][0], to_diffuse); ts.add(&s_cnt[k3][1], to_specular);
-		if (tid == 0 && it > 0) s_base[(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
-		__syncthreads();
+		warp_tally td, ts; td.add(&s_cnt[grp][k3][0], to_diffuse); ts.add(&s_cnt[grp][k3][1], to_specular);
+		if (leader && it > 0) s_base[grp][(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
+		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
 		if (it > 0) {   // the previous iteration's entries: its global base has arrived meanwhile
-			uint2 gb = s_base[(it - 1u) & 1u];
+			uint2 gb = s_base[grp][(it - 1u) & 1u];
 			if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
 			if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
 		}
-		if (tid == 0) {
-			uint32_t cd = s_cnt[k3][0], cs = s_cnt[k3][1];
+		if (leader) {
+			uint32_t cd = s_cnt[grp][k3][0], cs = s_cnt[grp][k3][1];
 			pending = (cd | cs) ? atomicAdd(cnt_pair, ((unsigned long long)cs << 32) | cd) : 0ull;
 			uint32_t kz = k3 == 0 ? 2u : k3 - 1u;   // (it + 2) % 3: idle until the iteration after next
-			s_cnt[kz][0] = 0; s_cnt[kz][1] = 0;
+			s_cnt[grp][kz][0] = 0; s_cnt[grp][kz][1] = 0;
 		}
 		p_d = to_diffuse; p_s = to_specular; p_ofs_d = td.ofs; p_ofs_s = ts.ofs; pslot = slot;
 		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u;
 		it++; k3 = k3 == 2 ? 0u : k3 + 1u;
 	}
 	if (it > 0) {
-		if (tid == 0) s_base[(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
-		__syncthreads();
-		uint2 gb = s_base[(it - 1u) & 1u];
+		if (leader) s_base[grp][(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
+		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
+		uint2 gb = s_base[grp][(it - 1u) & 1u];
 		if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
 		if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
 	}
@@ -302,14 +308,17 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	// into shared memory, reserved by ONE thread after the barrier and written in the FOLLOWING iteration;
 	// the shadow payload waits in shared memory meanwhile (st_pay), not in registers.
 	float4* st_pay = (float4*)(stage_base + PLU_STAGE_SHADE_IN);   // [2][5][PLU_CTA]: p|slot, w1|flags, c1, w2, c2
-	__shared__ uint32_t s_sh_cnt[3], s_n_cnt[3];
-	__shared__ uint2 s_base[2];   // (next-queue base, shadow-queue base)
-	if (tid < 3) { s_sh_cnt[tid] = 0; s_n_cnt[tid] = 0; }
+	constexpr bool WARP_SCOPE = !SMEM;   // group = CTA for staged scenes, warp otherwise (see k_extend)
+	const uint32_t lane = tid & 31u, grp = WARP_SCOPE ? (tid >> 5) : 0u;
+	const bool leader = WARP_SCOPE ? lane == 0 : tid == 0;
+	__shared__ uint32_t s_sh_cnt[PLU_CTA / 32][3], s_n_cnt[PLU_CTA / 32][3];
+	__shared__ uint2 s_base[PLU_CTA / 32][2];   // (next-queue base, shadow-queue base)
+	if (tid < (PLU_CTA / 32) * 3) { (&s_sh_cnt[0][0])[tid] = 0; (&s_n_cnt[0][0])[tid] = 0; }
 	__syncthreads();
-	uint32_t pending_sh = 0, pending_n = 0;   // thread 0
+	uint32_t pending_sh = 0, pending_n = 0;   // leader
 	uint32_t pslot = 0, p_ofs_n = 0, p_ofs_sh = 0, buf = 0, it = 0, k3 = 0; bool p_go = false, p_need = false;
 	auto flush = [&](uint32_t prev) {   // entries of iteration `prev`
-		uint2 gb = s_base[prev & 1u];
+		uint2 gb = s_base[grp][prev & 1u];
 		if (p_go) q_next[gb.x + p_ofs_n] = pslot;
 		if (CLS == CLS_DIFFUSE && p_need) {
 			const float4* row = st_pay + (size_t)(prev & 1u) * 5 * PLU_CTA + tid;
@@ -448,25 +457,25 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 		}
 		// count this iteration's batches; publish the bases of the previous one; ONE barrier
 		warp_tally tsh, tn; tsh.ofs = 0;
-		if (CLS == CLS_DIFFUSE) tsh.add(&s_sh_cnt[k3], need_entry);
-		tn.add(&s_n_cnt[k3], go_on);
-		if (tid == 0 && it > 0) s_base[(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
-		__syncthreads();
+		if (CLS == CLS_DIFFUSE) tsh.add(&s_sh_cnt[grp][k3], need_entry);
+		tn.add(&s_n_cnt[grp][k3], go_on);
+		if (leader && it > 0) s_base[grp][(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
+		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
 		if (it > 0) flush(it - 1u);
-		if (tid == 0) {   // the global atomics travel during the next iteration
-			uint32_t cn = s_n_cnt[k3], cs = CLS == CLS_DIFFUSE ? s_sh_cnt[k3] : 0u;
+		if (leader) {   // the global atomics travel during the next iteration
+			uint32_t cn = s_n_cnt[grp][k3], cs = CLS == CLS_DIFFUSE ? s_sh_cnt[grp][k3] : 0u;
 			pending_n = cn ? atomicAdd(cnt_next, cn) : 0u;
 			pending_sh = cs ? atomicAdd(cnt_shadow, cs) : 0u;
 			uint32_t kz = k3 == 0 ? 2u : k3 - 1u;   // (it + 2) % 3
-			s_n_cnt[kz] = 0; s_sh_cnt[kz] = 0;
+			s_n_cnt[grp][kz] = 0; s_sh_cnt[grp][kz] = 0;
 		}
 		p_go = go_on; p_ofs_n = tn.ofs; p_need = need_entry; p_ofs_sh = tsh.ofs; pslot = slot;
 		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u;
 		it++; k3 = k3 == 2 ? 0u : k3 + 1u;
 	}
 	if (it > 0) {
-		if (tid == 0) s_base[(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
-		__syncthreads();
+		if (leader) s_base[grp][(it - 1u) & 1u] = make_uint2(pending_n, pending_sh);
+		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
 		flush(it - 1u);
 	}
 }

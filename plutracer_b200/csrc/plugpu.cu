@@ -28,7 +28,7 @@ struct plu_gpu_ctx {
 	scene_ref sc{};
 	unsigned char* d_blob = nullptr;
 	float *d_tri_uv = nullptr, *d_tri_normal = nullptr, *d_texels = nullptr;
-	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr;
+	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr; float4* d_fast_leaf = nullptr;
 	bool blob_in_smem = false;
 	bool use_fast = false;
 	bool has_specular = false;     // any perfect-reflection / perfect-refraction / glass material
@@ -80,7 +80,7 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 
 static void free_scene(plu_gpu_ctx* ctx) {
 	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
-	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index);
+	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index); cudaFree(ctx->d_fast_leaf); ctx->d_fast_leaf = nullptr;
 	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
 	ctx->have_scene = false;
 }
@@ -164,6 +164,21 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 		std::vector<pluhost::fast_node_h> fn; std::vector<int32_t> fi;
 		pluhost::build_fast_bvh(d, fn, fi);
 		if (!fn.empty()) {
+			// leaf references carry their surface count; the surfaces are copied into leaf order (scene_dev.cuh)
+			for (auto& nd : fn)
+				for (int k = 0; k < 2; ++k)
+					if (nd.child[k] < 0) nd.child[k] = ~(((~nd.child[k]) << 3) | (nd.count[k] & 7));
+			std::vector<float> leaf(12 * fi.size(), 0.f);
+			for (size_t k = 0; k < fi.size(); ++k) {
+				int32_t s = fi[k], kind = d->prim_tag[s];
+				float* o = leaf.data() + 12 * k;
+				std::memcpy(o, d->prim_data + (size_t)s * 12, 12 * sizeof(float));
+				int32_t kr = (int32_t)(((uint32_t)kind << 30) | (uint32_t)rank[(size_t)s]);
+				std::memcpy(o + 7, &kr, 4);
+				std::memcpy(kind == PLU_PRIM_SPHERE ? o + 4 : o + 3, &s, 4);
+			}
+			CU(cudaMalloc(&ctx->d_fast_leaf, leaf.size() * sizeof(float)));
+			CU(cudaMemcpy(ctx->d_fast_leaf, leaf.data(), leaf.size() * sizeof(float), cudaMemcpyHostToDevice));
 			CU(cudaMalloc(&ctx->d_fast, fn.size() * sizeof(fast_node))); CU(cudaMemcpy(ctx->d_fast, fn.data(), fn.size() * sizeof(fast_node), cudaMemcpyHostToDevice));
 			CU(cudaMalloc(&ctx->d_fast_index, fi.size() * sizeof(int32_t))); CU(cudaMemcpy(ctx->d_fast_index, fi.data(), fi.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
 		}
@@ -173,7 +188,7 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 	ctx->use_fast = use_fast;
 	ctx->has_specular = false;
 	for (int32_t i = 0; i < d->n_materials; ++i) if (d->materials[i].tag >= PLU_MAT_PERFECT_REFLECTION && d->materials[i].tag <= PLU_MAT_GLASS) ctx->has_specular = true;
-	sc.fast_prim_index = ctx->d_fast_index;
+	sc.fast_prim_index = ctx->d_fast_index; sc.fast_leaf = ctx->d_fast_leaf;
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
 	ctx->have_scene = true;
