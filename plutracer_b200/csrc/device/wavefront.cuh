@@ -146,6 +146,43 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_
 	}
 }
 
+// What k_extend does with the outcome of scene->hit for one path: records the hit in the path record and
+// returns the material class whose queue the path joins (0: the path ends here).
+//   emission_material: the vertex adds Le (first vertex / after a specular bounce, renderer.cpp:66); its
+//   empty bsdf gives NEE = 0 and sampleF pdf = 0, i.e. the path ends (renderer.cpp:78)
+//   miss: renderer.cpp:87-90, after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
+//   a no-op unless T is not finite
+PLU_DEV int extend_finish(const scene_ref& sc, float4* recs, float4* rad, int bounce, uint32_t slot, const ray& r, int flags,
+                          bool hit, float t, int32_t prim, float nl) {
+	if (hit) {
+		int4 meta = sc.prim_meta(prim);   // kind, material, light, tie rank
+		int32_t mtag = sc.material(meta.y).tag;
+		if (mtag == PLU_MAT_EMISSION) {
+			bool le = bounce == 0 || (flags & FLAG_SPEC);
+			if (le || (flags & FLAG_NONFINITE)) {
+				f3 T = bounce == 0 ? mk3(1.f) : mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]);
+				f3 L = mk3(rad[slot]);
+				if (le) {
+					hit_rec hr; fill_record(sc, prim, meta.x, r, t, false, hr);
+					L = L + T * area_L(sc.light(meta.z), hr.norm, -r.d);
+				}
+				if (flags & FLAG_NONFINITE) L = L + T * (nl * mk3(0.f));
+				rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+			}
+			return 0;
+		}
+		float* rw = (float*)(recs + 4 * (size_t)slot);   // the .w words of quarters 2 and 3
+		rw[11] = t; rw[15] = __int_as_float(prim);
+		return mtag == PLU_MAT_DIFFUSE ? 1 : 2;
+	}
+	if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
+		f3 T = mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]); f3 L = mk3(rad[slot]);
+		for (int32_t i = 0; i < sc.n_lights; ++i) L = L + T * mk3(0.f);
+		rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+	}
+	return 0;
+}
+
 // ---- k_extend -------------------------------------------------------------------------------------------------
 // Loop skeleton shared by extend / shade / connect: iteration i computes on rows that were gathered
 // into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
@@ -209,37 +246,9 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 			ray r; r.e = mk3(o); r.d = mk3(d);
 			int flags = __float_as_int(d.w);
 			float t; int32_t prim;
-			if (trace_scene<COUNT, SMEM>(sc, r, o.w, t, prim, &tc)) {
-				int4 meta = sc.prim_meta(prim);   // kind, material, light, tie rank
-				int32_t mtag = sc.material(meta.y).tag;
-				if (mtag == PLU_MAT_EMISSION) {
-					// emission_material: the vertex adds Le (first vertex / after a specular bounce, renderer.cpp:66),
-					// its empty bsdf gives NEE = 0 and sampleF pdf = 0, i.e. the path ends here (renderer.cpp:78)
-					bool le = bounce == 0 || (flags & FLAG_SPEC);
-					if (le || (flags & FLAG_NONFINITE)) {
-						f3 T = bounce == 0 ? mk3(1.f) : mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]);
-						f3 L = mk3(wb.rad[slot]);
-						if (le) {
-							hit_rec hr; fill_record(sc, prim, meta.x, r, t, false, hr);
-							L = L + T * area_L(sc.light(meta.z), hr.norm, -r.d);
-						}
-						if (flags & FLAG_NONFINITE) L = L + T * (nl * mk3(0.f));
-						wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
-					}
-				} else {
-					float* rw = (float*)(recs + 4 * (size_t)slot);   // the .w words of quarters 2 and 3
-					rw[11] = t; rw[15] = __int_as_float(prim);
-					to_diffuse = mtag == PLU_MAT_DIFFUSE; to_specular = !to_diffuse;
-				}
-			} else {
-				// renderer.cpp:87-90: after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
-				// a no-op unless T is not finite
-				if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
-					f3 T = mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]); f3 L = mk3(wb.rad[slot]);
-					for (int32_t i = 0; i < sc.n_lights; ++i) L = L + T * mk3(0.f);
-					wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
-				}
-			}
+			bool hit = trace_scene<COUNT, SMEM>(sc, r, o.w, t, prim, &tc);
+			int cls = extend_finish(sc, recs, wb.rad, bounce, slot, r, flags, hit, t, prim, nl);
+			to_diffuse = cls == 1; to_specular = cls == 2;
 		}
 		warp_tally td, ts; td.add(&s_cnt[grp][k3][0], to_diffuse); ts.add(&s_cnt[grp][k3][1], to_specular);
 		if (leader && it > 0) s_base[grp][(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
