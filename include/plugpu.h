@@ -211,6 +211,28 @@ int plu_gpu_trace_rays(plu_gpu_ctx* ctx, int64_t n, const float* origin3, const 
 int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params* p, int64_t pixel_begin,
                             int64_t pixel_count, float* out_rgb);
 
+/* ---- post-process + image write: the step right after the path (main.cpp:183, :209) -------- */
+enum {
+	PLU_POST_TONEMAP = 1u << 0   /* apply postprocesser::postprocess before quantising             */
+};
+/* postprocesser::postprocess (main.cpp:76-111): white-preserving luma Reinhard (white = 2) and
+ * gamma 1/2.2 over a HOST float RGB image, in place.  pow is evaluated in double and rounded to
+ * float (host powf differs from it in the last bit for a vanishing fraction of inputs).        */
+int plu_gpu_postprocess(plu_gpu_ctx* ctx, int32_t width, int32_t height, float* rgb_inout);
+/* Size of the .bmp file texture2d::write_bmp produces for a W x H image (texture.cpp:167-173).  */
+int64_t plu_bmp_size(int32_t width, int32_t height);
+/* texture2d::write_bmp (texture.cpp:178-194) without the file: clamp to [0,1], byte =
+ * (unsigned char)(c * 255), 24-bit BGR bottom-up rows padded to 4 bytes behind the 54-byte
+ * header.  rgb: HOST float image; with PLU_POST_TONEMAP the tone map is fused in front (the
+ * float image itself is not modified).  out_bmp: HOST, at least plu_bmp_size bytes.             */
+int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t width, int32_t height, const float* rgb,
+                       uint32_t flags, unsigned char* out_bmp, int64_t cap);
+/* Same from a DEVICE framebuffer (e.g. the one plu_gpu_render_device filled): tone map +
+ * quantise + BMP layout in one kernel, only the bytes travel to the host (3 instead of 12 per
+ * pixel).  Work is enqueued on `stream` (NULL = the context's) and synchronised.               */
+int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t width, int32_t height, const float* d_rgb,
+                              uint32_t flags, void* stream, unsigned char* out_bmp, int64_t cap);
+
 /* ---- host-side scene plumbing (no GPU needed) --------------------------------------------- */
 typedef struct plu_scene plu_scene;   /* owns the arrays a plu_scene_desc points at              */
 

@@ -39,4 +39,9 @@ g++ -std=gnu++14 -O2 -fpermissive -w \
     -include "$here/ref_prelude.h" \
     -I"$shim" -I"$ref/inc" -I"$ref/depd/glm" -I"$ref/src" -I"$here/../include" -I"$here/../plutracer_b200/csrc/host" \
     "$here/ref_driver.cpp" -o "$out/plu_ref" -lpthread
-echo "build_ref: built $out/plu_ref"
+# the reference's post-process (main.cpp:76-112) + BMP writer (texture.cpp:178-194), main.cpp included as a TU
+g++ -std=gnu++14 -O2 -fpermissive -w \
+    -include "$here/ref_prelude.h" \
+    -I"$shim" -I"$ref/inc" -I"$ref/depd/glm" -I"$ref/src" \
+    "$here/ref_post_driver.cpp" -o "$out/plu_ref_post" -lpthread
+echo "build_ref: built $out/plu_ref $out/plu_ref_post"

@@ -37,6 +37,15 @@ int orc_render_mt(const plu_scene_desc* d, int32_t width, int32_t height, int32_
                   uint32_t seed, int32_t x0, int32_t y0, int32_t x1, int32_t y1, int trig,
                   int x_first, float* img, float* per_sample);
 
+/* postprocesser::postprocess (main.cpp:76-111): white-preserving luma Reinhard (white = 2) + gamma 1/2.2,
+ * in place over n pixels.  pow_mode: 0 = powf of the host libm (what the compiled reference runs),
+ * 1 = double pow rounded to float (what the CUDA path computes). */
+void orc_postprocess(int64_t n_pixels, float* rgb, int pow_mode);
+/* texture2d::write_bmp (texture.cpp:178-194) + stbi_write_bmp (:167-173): the bytes of the .bmp file
+ * (54-byte header, 24-bit BGR, bottom-up, rows padded to 4 bytes).  Returns the byte count; writes at
+ * most cap bytes. */
+int64_t orc_encode_bmp(int32_t width, int32_t height, const float* rgb, unsigned char* out, int64_t cap);
+
 void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 /* det trig for tests: which = 0 sin, 1 cos, 2 acos */
 void orc_det_trig(int which, int64_t n, const float* x, float* y);

@@ -6,6 +6,6 @@ library raises.
 """
 from . import _ffi  # noqa: F401
 from ._build import build_lib  # noqa: F401
-from .renderer import DEFAULT_SEED, GpuContext, renderer  # noqa: F401
+from .renderer import DEFAULT_SEED, GpuContext, postprocesser, renderer, write_bmp  # noqa: F401
 from .scene import Scene, stratified_sampler, texture2d  # noqa: F401
 from .shard import reduce_framebuffer, shard_plan, sharded_renderer  # noqa: F401

@@ -17,6 +17,7 @@ RENDER_BVH_REFERENCE = 2
 RENDER_COUNT_BVH = 4
 RENDER_BVH_FAST = 8
 RENDER_PROFILE = 16
+POST_TONEMAP = 1
 
 
 class CameraDesc(C.Structure):
@@ -76,6 +77,10 @@ SYMBOLS = {
     "plu_gpu_trace_primary": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P, _P]),
     "plu_gpu_trace_rays": (C.c_int, [_P, C.c_int64, _P, _P, C.c_uint32, _P, _P, _P]),
     "plu_gpu_sample_radiance": (C.c_int, [_P, C.POINTER(RenderParams), C.c_int64, C.c_int64, _P]),
+    "plu_gpu_postprocess": (C.c_int, [_P, C.c_int32, C.c_int32, _P]),
+    "plu_bmp_size": (C.c_int64, [C.c_int32, C.c_int32]),
+    "plu_gpu_encode_bmp": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, C.c_int64]),
+    "plu_gpu_encode_bmp_device": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, _P, C.c_int64]),
     "plu_scene_load_urn": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_load_flat": (C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_save_flat": (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, C.c_int32, C.c_char_p]),

@@ -3,6 +3,7 @@
 // drop-in boundary of SURVEY.md 8b.  There is no CPU fallback: every entry point that needs the GPU
 // fails with PLU_E_CUDA when no device is usable.
 #include "device/wavefront.cuh"
+#include "device/post.cuh"
 #include "host/bvh_build.h"
 #include "host/scene_store.h"
 #include <algorithm>
@@ -493,6 +494,73 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 		p0 += np;
 	}
 	return PLU_OK;
+}
+
+// ---- post-process + image write (main.cpp:183, :209) -------------------------------------------------------------
+extern "C" int64_t plu_bmp_size(int32_t w, int32_t h) {
+	if (w <= 0 || h <= 0) return 0;
+	return 54 + ((int64_t)w * 3 + ((-w * 3) & 3)) * h;
+}
+
+static void bmp_header(int32_t W, int32_t H, unsigned char* o) {   // stbi_write_bmp, texture.cpp:167-173
+	std::memset(o, 0, 54);
+	auto put32 = [&](int at, uint32_t v) { o[at] = v & 255; o[at + 1] = (v >> 8) & 255; o[at + 2] = (v >> 16) & 255; o[at + 3] = (v >> 24) & 255; };
+	o[0] = 'B'; o[1] = 'M'; put32(2, (uint32_t)plu_bmp_size(W, H)); put32(10, 14 + 40);
+	put32(14, 40); put32(18, (uint32_t)W); put32(22, (uint32_t)H); o[26] = 1; o[28] = 24;
+}
+
+extern "C" int plu_gpu_postprocess(plu_gpu_ctx* ctx, int32_t w, int32_t h, float* rgb) {
+	if (!ctx) return PLU_E_ARG;
+	if (w <= 0 || h <= 0 || !rgb) return fail(ctx, PLU_E_ARG, "bad image arguments");
+	CU(cudaSetDevice(ctx->device));
+	size_t floats = (size_t)w * h * 3;
+	if (ctx->fb_floats < floats) {
+		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
+		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
+	}
+	CU(cudaMemcpyAsync(ctx->d_fb, rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	int64_t n = (int64_t)w * h;
+	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+	k_tonemap<<<grid, 256, 0, ctx->stream>>>(n, ctx->d_fb);
+	CU(cudaGetLastError());
+	CU(cudaMemcpyAsync(rgb, ctx->d_fb, floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t w, int32_t h, const float* d_rgb, uint32_t flags, void* stream,
+                                         unsigned char* out, int64_t cap) {
+	if (!ctx) return PLU_E_ARG;
+	if (w <= 0 || h <= 0 || !d_rgb || !out) return fail(ctx, PLU_E_ARG, "bad image arguments");
+	const int64_t total = plu_bmp_size(w, h);
+	if (cap < total) return fail(ctx, PLU_E_ARG, "output buffer smaller than plu_bmp_size");
+	CU(cudaSetDevice(ctx->device));
+	cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+	unsigned char* d_body = nullptr;
+	CU(cudaMalloc(&d_body, (size_t)(total - 54)));
+	int64_t n = (int64_t)w * h;
+	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+	k_encode_bmp<<<grid, 256, 0, st>>>(w, h, d_rgb, (flags & PLU_POST_TONEMAP) ? 1 : 0, d_body);
+	cudaError_t e = cudaGetLastError();
+	if (e == cudaSuccess) e = cudaMemcpyAsync(out + 54, d_body, (size_t)(total - 54), cudaMemcpyDeviceToHost, st);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+	cudaFree(d_body);
+	if (e != cudaSuccess) return fail(ctx, PLU_E_CUDA, std::string("bmp encode: ") + cudaGetErrorString(e));
+	bmp_header(w, h, out);
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t w, int32_t h, const float* rgb, uint32_t flags, unsigned char* out, int64_t cap) {
+	if (!ctx) return PLU_E_ARG;
+	if (w <= 0 || h <= 0 || !rgb || !out) return fail(ctx, PLU_E_ARG, "bad image arguments");
+	CU(cudaSetDevice(ctx->device));
+	size_t floats = (size_t)w * h * 3;
+	if (ctx->fb_floats < floats) {
+		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
+		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
+	}
+	CU(cudaMemcpyAsync(ctx->d_fb, rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	return plu_gpu_encode_bmp_device(ctx, w, h, ctx->d_fb, flags, ctx->stream, out, cap);
 }
 
 // ---- host-side helpers ------------------------------------------------------------------------------------------

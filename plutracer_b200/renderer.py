@@ -83,6 +83,30 @@ class GpuContext:
         self._check(self._lib.plu_gpu_sample_radiance(self._h, C.byref(params), pixel_begin, pixel_count, out.ctypes.data))
         return out
 
+    def postprocess(self, rgb):
+        """postprocesser::postprocess (main.cpp:88-111) on a host float32 (H, W, 3) image, in place."""
+        assert rgb.dtype == np.float32 and rgb.flags.c_contiguous and rgb.ndim == 3 and rgb.shape[2] == 3
+        self._check(self._lib.plu_gpu_postprocess(self._h, rgb.shape[1], rgb.shape[0], rgb.ctypes.data))
+        return rgb
+
+    def encode_bmp(self, rgb, tonemap=False, device_ptr=None, size=None, stream=None):
+        """The bytes texture2d::write_bmp (texture.cpp:178-194) writes, from a host float32 (H, W, 3) image or,
+        with device_ptr + size=(W, H), from a device framebuffer; tonemap=True fuses the post-process in front."""
+        flags = _ffi.POST_TONEMAP if tonemap else 0
+        if device_ptr is None:
+            assert rgb.dtype == np.float32 and rgb.flags.c_contiguous and rgb.ndim == 3 and rgb.shape[2] == 3
+            W, H = rgb.shape[1], rgb.shape[0]
+        else:
+            W, H = int(size[0]), int(size[1])
+        n = self._lib.plu_bmp_size(W, H)
+        out = np.zeros(n, np.uint8)
+        if device_ptr is None:
+            self._check(self._lib.plu_gpu_encode_bmp(self._h, W, H, rgb.ctypes.data, flags, out.ctypes.data, n))
+        else:
+            self._check(self._lib.plu_gpu_encode_bmp_device(self._h, W, H, C.c_void_p(int(device_ptr)), flags,
+                                                            C.c_void_p(int(stream) if stream else None), out.ctypes.data, n))
+        return out
+
     def close(self):
         if self._h:
             self._lib.plu_gpu_destroy(self._h)
@@ -119,3 +143,22 @@ class renderer:
         p = GpuContext.params(W, H, self.main_sampler.sample_count[0], self.seed, self.flags)
         self.last_stats = self.ctx.render(p, target.pixels)
         return self.last_stats
+
+
+class postprocesser:
+    """Drop-in for plu::postprocesser (main.cpp:76-112): postprocess(rt) tone-maps the render target in place."""
+
+    def __init__(self, ctx=None, device=0):
+        self.ctx = ctx if ctx is not None else GpuContext(device)
+
+    def postprocess(self, rt):
+        self.ctx.postprocess(rt.pixels)
+
+
+def write_bmp(rt, filename, ctx=None, device=0):
+    """texture2d::write_bmp(filename) (texture.cpp:178-194) with the clamp / quantise / layout on the GPU."""
+    ctx = ctx if ctx is not None else GpuContext(device)
+    data = ctx.encode_bmp(rt.pixels)
+    with open(filename, "wb") as f:
+        f.write(data.tobytes())
+    return len(data)

@@ -117,6 +117,21 @@ class Oracle:
         assert rc == 0
         return img, ps
 
+    def postprocess(self, rgb, pow_mode=0):
+        out = np.ascontiguousarray(rgb, np.float32).copy()
+        self.lib.orc_postprocess(C.c_int64(out.shape[0] * out.shape[1]), self._p(out), int(pow_mode))
+        return out
+
+    def encode_bmp(self, rgb):
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        h, w = rgb.shape[:2]
+        self.lib.orc_encode_bmp.restype = C.c_int64
+        cap = 54 + (w * 3 + ((-w * 3) & 3)) * h
+        out = np.zeros(cap, np.uint8)
+        n = self.lib.orc_encode_bmp(w, h, self._p(rgb), self._p(out), C.c_int64(cap))
+        assert n == cap
+        return out
+
     def philox(self, ctr, key):
         c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
         self.lib.orc_philox4x32_10(c, k, o)
