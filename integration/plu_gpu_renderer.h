@@ -229,4 +229,30 @@ struct gpu_renderer {
 		if (plu_gpu_render(ctx, &p, rgb, nullptr) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
 	}
 };
+
+// Drop-in for plu::postprocesser (main.cpp:76-112): same postprocess(shared_ptr<texture2d>) call.
+struct gpu_postprocesser {
+	void postprocess(shared_ptr<texture2d> rt) {
+		plu_gpu_ctx* ctx = nullptr;
+		if (plu_gpu_create(0, &ctx) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
+		struct guard { plu_gpu_ctx* c; ~guard() { plu_gpu_destroy(c); } } g{ctx};
+		if (plu_gpu_postprocess(ctx, (int32_t)rt->size.x, (int32_t)rt->size.y, &rt->pixel(uvec2(0, 0)).x) != PLU_OK)
+			throw std::runtime_error(plu_gpu_last_error(ctx));
+	}
+};
+
+// texture2d::write_bmp(filename) (texture.cpp:178-194) with clamp / quantise / BMP layout on the device.
+inline void gpu_write_bmp(shared_ptr<texture2d> rt, const std::string& filename) {
+	plu_gpu_ctx* ctx = nullptr;
+	if (plu_gpu_create(0, &ctx) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
+	struct guard { plu_gpu_ctx* c; ~guard() { plu_gpu_destroy(c); } } g{ctx};
+	int64_t n = plu_bmp_size((int32_t)rt->size.x, (int32_t)rt->size.y);
+	std::vector<unsigned char> bytes((size_t)n);
+	if (plu_gpu_encode_bmp(ctx, (int32_t)rt->size.x, (int32_t)rt->size.y, &rt->pixel(uvec2(0, 0)).x, 0, bytes.data(), n) != PLU_OK)
+		throw std::runtime_error(plu_gpu_last_error(ctx));
+	FILE* f = fopen(filename.c_str(), "wb");
+	if (!f) throw std::runtime_error("cannot open " + filename);
+	fwrite(bytes.data(), 1, bytes.size(), f);
+	fclose(f);
+}
 }  // namespace plu
