@@ -25,32 +25,37 @@ def sass_rows(rep, which):
     return blocks[which]
 
 
-def line_table(so, kernel):
+def line_table(so, kernel, outer=False):
     tmp = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, capture_output=True)
     lines = []
     for f in sorted(os.listdir(tmp)):
         if not f.endswith(".cubin"):
             continue
-        dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
-        inside, cur = False, ("?", 0)
+        dis = subprocess.run(["nvdisasm", "-gi" if outer else "-g", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
+        inside, cur, fresh = False, ("?", 0), True
         for l in dis.splitlines():
             if l.startswith("//---") and ".text." in l:
                 inside = kernel in l
                 continue
             if not inside:
                 continue
-            m = re.search(r'//## File "([^"]+)", line (\d+)', l)
+            m = re.search(r'//## File "([^"]+)", line (\d+)(?: inlined at "([^"]+)", line (\d+))?', l)
             if m:
-                cur = (os.path.basename(m.group(1)), int(m.group(2))); continue
+                if outer and m.group(3):   # the chain ends at the outermost call site
+                    cur = (os.path.basename(m.group(3)), int(m.group(4)))
+                elif not outer or fresh:
+                    cur = (os.path.basename(m.group(1)), int(m.group(2)))
+                fresh = False
+                continue
             if re.match(r"\s+/\*[0-9a-f]{4,5}\*/", l):
-                lines.append(cur)
+                lines.append(cur); fresh = True
     return lines
 
 
-def main(rep, so, kernel, which=0, top=40):
+def main(rep, so, kernel, which=0, top=40, outer=False):
     b = sass_rows(rep, which)
-    lt = line_table(so, kernel)
+    lt = line_table(so, kernel, outer)
     h = b["hdr"]
     iN, iE = h.index("# Samples"), h.index("Instructions Executed")
     print(b["name"][:90], "| sass rows", len(b["rows"]), "| disasm rows", len(lt))
@@ -66,5 +71,5 @@ def main(rep, so, kernel, which=0, top=40):
 
 
 if __name__ == "__main__":
-    a = sys.argv
-    main(a[1], a[2], a[3], int(a[4]) if len(a) > 4 else 0, int(a[5]) if len(a) > 5 else 40)
+    a = [x for x in sys.argv if x != "--outer"]   # --outer: attribute inlined code to the outermost call site
+    main(a[1], a[2], a[3], int(a[4]) if len(a) > 4 else 0, int(a[5]) if len(a) > 5 else 40, "--outer" in sys.argv)
