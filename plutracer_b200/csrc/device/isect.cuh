@@ -263,11 +263,25 @@ PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bou
 // d == 0 on that axis) drop out of fminf/fmaxf, i.e. count as "inside".  What it does NOT reproduce is
 // the reference losing a true hit because one of its own origin-inflated ancestor boxes rejects the
 // ray by rounding; tests compare both walks on every named scene and on the synthetic ones.
+// Packed fp32 pairs (sm_100 FADD2 / FMUL2: two IEEE round-to-nearest results per issue slot): the plane
+// distances of BOTH children of a fast node along one axis side are one subtract + one multiply.
+PLU_DEV unsigned long long pk2(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+PLU_DEV void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+PLU_DEV unsigned long long submul2(unsigned long long m, unsigned long long e, unsigned long long i) {
+	unsigned long long t;
+	asm("{\n\t.reg .b64 d;\n\tsub.rn.f32x2 d, %1, %2;\n\tmul.rn.f32x2 %0, d, %3;\n\t}" : "=l"(t) : "l"(m), "l"(e), "l"(i));
+	return t;
+}
+PLU_DEV float fmin3f(float a, float b, float c) { float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+
 template <bool COUNT>
 PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc) {
 	const fast_node* nodes = sc.fast_nodes;
 	const float4* leaves = sc.fast_leaf;   // 3 x float4 per leaf slot, in leaf order (plugpu.cu: upload)
 	const float ix = 1.f / r.d.x, iy = 1.f / r.d.y, iz = 1.f / r.d.z;
+	const unsigned long long ex2 = pk2(r.e.x, r.e.x), ey2 = pk2(r.e.y, r.e.y), ez2 = pk2(r.e.z, r.e.z);
+	const unsigned long long ix2 = pk2(ix, ix), iy2 = pk2(iy, iy), iz2 = pk2(iz, iz);
 	float best_t = 3.0e38f; int32_t best = -1, best_rank = -1;
 	// child reference: >= 0 inner node index; < 0 leaf ~((first_slot << 3) | count); DONE = stack exhausted
 	const int32_t DONE = (int32_t)0x80000000;
@@ -282,14 +296,13 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 			float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c); int4 d = __ldg(&nd->d);
 			if (COUNT) tc->nodes++;
 			float cull = best_t + fabsf(best_t) * 1e-5f;
-			// child 0: min a.xyz, max (a.w, b.x, b.y);  child 1: min (b.z, b.w, c.x), max c.yzw
-			float t1, t2, n0, f0, n1, f1;
-			t1 = (a.x - r.e.x) * ix; t2 = (a.w - r.e.x) * ix; n0 = fminf(t1, t2); f0 = fmaxf(t1, t2);
-			t1 = (a.y - r.e.y) * iy; t2 = (b.x - r.e.y) * iy; n0 = fmaxf(n0, fminf(t1, t2)); f0 = fminf(f0, fmaxf(t1, t2));
-			t1 = (a.z - r.e.z) * iz; t2 = (b.y - r.e.z) * iz; n0 = fmaxf(n0, fminf(t1, t2)); f0 = fminf(f0, fmaxf(t1, t2));
-			t1 = (b.z - r.e.x) * ix; t2 = (c.y - r.e.x) * ix; n1 = fminf(t1, t2); f1 = fmaxf(t1, t2);
-			t1 = (b.w - r.e.y) * iy; t2 = (c.z - r.e.y) * iy; n1 = fmaxf(n1, fminf(t1, t2)); f1 = fminf(f1, fmaxf(t1, t2));
-			t1 = (c.x - r.e.z) * iz; t2 = (c.w - r.e.z) * iz; n1 = fmaxf(n1, fminf(t1, t2)); f1 = fminf(f1, fmaxf(t1, t2));
+			// (child 0, child 1) pairs: a = min.x min.y, b = min.z max.x, c = max.y max.z  (plugpu.cu: upload)
+			float lx0, lx1, ly0, ly1, lz0, lz1, hx0, hx1, hy0, hy1, hz0, hz1;
+			upk2(submul2(pk2(a.x, a.y), ex2, ix2), lx0, lx1); upk2(submul2(pk2(a.z, a.w), ey2, iy2), ly0, ly1);
+			upk2(submul2(pk2(b.x, b.y), ez2, iz2), lz0, lz1); upk2(submul2(pk2(b.z, b.w), ex2, ix2), hx0, hx1);
+			upk2(submul2(pk2(c.x, c.y), ey2, iy2), hy0, hy1); upk2(submul2(pk2(c.z, c.w), ez2, iz2), hz0, hz1);
+			float n0 = fmax3f(fminf(lx0, hx0), fminf(ly0, hy0), fminf(lz0, hz0)), f0 = fmin3f(fmaxf(lx0, hx0), fmaxf(ly0, hy0), fmaxf(lz0, hz0));
+			float n1 = fmax3f(fminf(lx1, hx1), fminf(ly1, hy1), fminf(lz1, hz1)), f1 = fmin3f(fmaxf(lx1, hx1), fmaxf(ly1, hy1), fmaxf(lz1, hz1));
 			bool h0 = !(f0 < n0) && !(f0 < 0.f) && !(n0 > cull);
 			bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull);
 			if (h0 && h1) {

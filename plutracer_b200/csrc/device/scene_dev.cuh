@@ -19,7 +19,8 @@ namespace plud {
 struct ref_node { float4 lo, hi; };
 
 // Tight two-child node of the fast BVH (host/bvh_build.cpp), 64 B = four 128-bit loads:
-//   a = (c0.min.xyz, c0.max.x)  b = (c0.max.yz, c1.min.xy)  c = (c1.min.z, c1.max.xyz)
+//   (child 0, child 1) pairs, so that one packed fp32x2 instruction serves both children:
+//   a = (min.x0 min.x1 min.y0 min.y1)  b = (min.z0 min.z1 max.x0 max.x1)  c = (max.y0 max.y1 max.z0 max.z1)
 //   d = (child0, child1, -, -) as int: >= 0 inner node index, < 0 leaf: ~((first_leaf_slot << 3) | count)
 // Leaf slots hold the surfaces themselves in leaf order (fast_leaf, 3 x float4 each), so a leaf test is one
 // dependent load level instead of index -> meta -> data:

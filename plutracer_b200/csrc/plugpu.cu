@@ -166,9 +166,16 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 		pluhost::build_fast_bvh(d, fn, fi);
 		if (!fn.empty()) {
 			// leaf references carry their surface count; the surfaces are copied into leaf order (scene_dev.cuh)
-			for (auto& nd : fn)
+			for (auto& nd : fn) {
 				for (int k = 0; k < 2; ++k)
 					if (nd.child[k] < 0) nd.child[k] = ~(((~nd.child[k]) << 3) | (nd.count[k] & 7));
+				// builder order: c0.min, c0.max, c1.min, c1.max  ->  device order: (child 0, child 1) pairs per plane
+				float f[12]; std::memcpy(f, nd.f, sizeof(f));
+				for (int ax = 0; ax < 3; ++ax) {
+					nd.f[2 * ax] = f[ax]; nd.f[2 * ax + 1] = f[6 + ax];             // min planes
+					nd.f[6 + 2 * ax] = f[3 + ax]; nd.f[6 + 2 * ax + 1] = f[9 + ax];   // max planes
+				}
+			}
 			std::vector<float> leaf(12 * fi.size(), 0.f);
 			for (size_t k = 0; k < fi.size(); ++k) {
 				int32_t s = fi[k], kind = d->prim_tag[s];
