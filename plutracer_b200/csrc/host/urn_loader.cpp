@@ -13,7 +13,9 @@
 #include <array>
 #include <cctype>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <functional>
 #include <list>
@@ -86,6 +88,38 @@ public:
 };
 
 // ---- values -------------------------------------------------------------------------------------------
+// texture2d::texture2d(bmp_filename), texture.cpp:4-65, restated with its quirks: 24-bit uncompressed only; the
+// pixel loop runs i = imageSize, imageSize-3, .., 3 over data[i], data[i+1], data[i+2], so texel j is the BMP
+// pixel imageSize/3 - j (the image comes out rotated by 180 degrees and shifted by one pixel), row padding bytes
+// are taken for pixels, the first pixel of the file is never used and texel 0 is read one pixel PAST the buffer
+// (heap garbage in the reference; 0 here).  Appends width*height texels (what texture2d::texel can address).
+static bool load_bmp_texels(const std::string& path, std::vector<float>& out, int32_t& width, int32_t& height) {
+	FILE* f = fopen(path.c_str(), "rb");
+	if (!f) return false;
+	unsigned char header[54];
+	if (fread(header, 1, 54, f) != 54 || header[0] != 'B' || header[1] != 'M') { fclose(f); throw parse_error("invalid BMP file '" + path + "'"); }
+	auto i32 = [&](int at) { int32_t v; std::memcpy(&v, header + at, 4); return v; };
+	if (i32(0x1E) != 0 || i32(0x1C) != 24) { fclose(f); throw parse_error("Not a correct BMP file '" + path + "' (24 bpp, uncompressed)"); }
+	uint32_t image_size = (uint32_t)i32(0x22);
+	width = i32(0x12); height = i32(0x16);
+	if (width <= 0 || height <= 0 || (int64_t)width * height > (int64_t)1 << 28) { fclose(f); throw parse_error("bad BMP size in '" + path + "'"); }
+	if (image_size == 0) image_size = (uint32_t)width * (uint32_t)height * 3u;
+	std::vector<unsigned char> data((size_t)image_size + 3, 0);   // +3: the out-of-bounds pixel reads as 0
+	size_t got = fread(data.data(), 1, image_size, f);   // the reference reads from the current position (54), ignoring dataPos
+	(void)got;
+	fclose(f);
+	size_t n_px = image_size / 3, want = (size_t)width * (size_t)height, j = 0;
+	size_t base = out.size();
+	out.resize(base + want * 3, 0.f);
+	for (int64_t i = (int64_t)image_size; i > 0 && j < want; i -= 3, ++j) {
+		out[base + 3 * j + 0] = (float)data[(size_t)i + 2] / 255.f;   // d.r
+		out[base + 3 * j + 1] = (float)data[(size_t)i + 1] / 255.f;   // d.g
+		out[base + 3 * j + 2] = (float)data[(size_t)i] / 255.f;       // d.b
+	}
+	(void)n_px;
+	return true;
+}
+
 struct value;
 using value_list = std::vector<value>;
 struct func_t;
@@ -384,8 +418,13 @@ struct builder {
 				t.tag = PLU_TEX_GRID; put(t.c0, block_to_v3(cx, ts[1])); put(t.c1, block_to_v3(cx, ts[2]));
 				t.scale = (float)cx.eval(ts[3]).num();
 				value l = cx.eval(ts[4]); if (l.type != value::Float) throw parse_error("grid line size must be a Float"); t.line = (float)l.f;
-			} else if (kind == "img") {
-				throw parse_error("img textures: BMP decoding is not part of the render path boundary; pass texels through plu_scene_desc");
+			} else if (kind == "img" && ts.size() >= 2) {
+				const std::string& file = ts[1].str();
+				int32_t w = 0, h = 0;
+				t.tag = PLU_TEX_IMAGE; t.img_offset = (int32_t)(out.image_texels.size() / 3);
+				if (!load_bmp_texels(file, out.image_texels, w, h) && !load_bmp_texels(base_dir + file, out.image_texels, w, h))
+					throw parse_error("cannot read BMP file '" + file + "'");
+				t.img_w = w; t.img_h = h;
 			} else throw parse_error("unknown texture '" + kind + "'");
 			pm.has_tex = true; pm.t = t; m.texture = 0;
 			m.color[0] = m.color[1] = m.color[2] = 0.f;   // props::color(tex) : col(0.f)

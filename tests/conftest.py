@@ -35,5 +35,5 @@ def gpu(lib):
 
 
 REF_SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's scenes (BASELINE.json configs)
-OWN_SCENES = ["atrium", "colonnade", "shard"]                          # scenes/ of this repo
+OWN_SCENES = ["atrium", "colonnade", "shard", "gallery"]                         # scenes/ of this repo
 SCENES = REF_SCENES + OWN_SCENES

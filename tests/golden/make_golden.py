@@ -30,7 +30,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "plu_ref")
 REF_SCENES = os.environ.get("PLU_REFERENCE", "/root/reference") + "/scenes"
 SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's own scenes/ (BASELINE.json configs)
-OWN_SCENES = ["atrium", "colonnade", "shard"]   # this repo's scenes/: all material kinds, scripted objects + lens, triangle mesh
+OWN_SCENES = ["atrium", "colonnade", "shard", "gallery"]   # this repo's scenes/: all material kinds, scripted objects + lens, triangle mesh
 PW, PH = 96, 72
 SW, SH, SN, SSEED = 32, 24, 2, 7
 
@@ -74,6 +74,7 @@ def make_rays(scene_npz_primary, rng, n=4096):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--converged", action="store_true")
+    ap.add_argument("--only", default="", help="regenerate one scene only (own seeded ray set)")
     ap.add_argument("--big", default="", help="path of a pre-rendered cornell 256x256 /smp 64 pair prefix (a/b .bin)")
     args = ap.parse_args()
     if not os.path.exists(REF_BIN):
@@ -81,7 +82,11 @@ def main():
     tmp = "/tmp/plu_golden"
     os.makedirs(tmp, exist_ok=True)
     rng = np.random.default_rng(20261104)
-    for s in SCENES + OWN_SCENES:
+    todo = SCENES + OWN_SCENES
+    if args.only:
+        todo = [args.only]
+        rng = np.random.default_rng(20261104 + sum(map(ord, args.only)))
+    for s in todo:
         own = s in OWN_SCENES
         urn = f"{ROOT}/scenes/{s}.urn" if own else f"{REF_SCENES}/{s}.urn"
         cwd = f"{ROOT}/scenes" if own else None   # the reference opens triangle-mesh files relative to the cwd

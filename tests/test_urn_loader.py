@@ -23,7 +23,17 @@ def test_own_scenes_load_like_the_reference(lib, tmp_path, name):
     (collect-range / block-format / concat-all / reduce / +), a lens camera, a triangle mesh"""
     from plutracer_b200 import Scene
     sc = Scene.load_urn(os.path.join(ROOT, "scenes", name + ".urn"))
-    assert _flat_bytes(sc, tmp_path) == open(os.path.join(GOLDEN, name + ".pluscene"), "rb").read()
+    got, want = _flat_bytes(sc, tmp_path), open(os.path.join(GOLDEN, name + ".pluscene"), "rb").read()
+    if name == "gallery":
+        # `img` texture (texture.cpp:4-65): the reference reads texel 0 one pixel past its buffer (heap bytes);
+        # the loader here yields 0 for it.  Everything else — the 180-degree rotation and one-pixel shift of
+        # the decode included — is byte-identical.
+        n_tex = sc.desc.n_image_texels
+        assert n_tex == 12 * 8 and len(got) == len(want)
+        t0 = len(got) - 12 * n_tex
+        assert got[:t0] == want[:t0] and got[t0 + 12:] == want[t0 + 12:]
+        return
+    assert got == want
 
 
 @pytest.mark.parametrize("name", REF_SCENES + ["minimal1", "test", "test1"])
