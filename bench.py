@@ -184,6 +184,7 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     warm = max(args.warmup, 3)
 
