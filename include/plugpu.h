@@ -187,6 +187,38 @@ const char* plu_gpu_last_error(const plu_gpu_ctx* ctx);
  * the material/light/texture object graphs and bvh_tree construction (main.cpp:168-171).        */
 int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* scene);
 
+/* Where the traversal structures are built.  The reference builds its tree on the host with a
+ * recursive median split (bvh_tree.cpp:7-36: round-robin axis, std::sort by box centre, halves);
+ * PLU_BUILD_DEVICE builds the same tree — same leaf order, hence same tie ranks — and the fast
+ * BVH with CUDA kernels, level by level; PLU_BUILD_HOST keeps the host
+ * restatement (host/bvh_build.cpp).  Both produce byte-identical device tables.                */
+enum { PLU_BUILD_DEVICE = 0u, PLU_BUILD_HOST = 1u };
+
+typedef struct plu_build_stats {
+	double  ms_total;            /* wall clock of the structure build inside the upload          */
+	double  ms_ref_order;        /* reference leaf order (tie ranks)                             */
+	double  ms_ref_nodes;        /* reference tree, pre-order with skip links                    */
+	double  ms_fast_bvh;         /* binned-SAH BVH + leaf records                                */
+	int32_t levels_ref;          /* sort levels of the median split                              */
+	int32_t levels_fast;         /* levels of the SAH build                                      */
+	int32_t host_tie_segments;   /* segments (> 16 surfaces, equal box centres) whose order the
+	                                host's std::sort had to decide (bvh_tree.cpp:23 is unstable) */
+	int32_t n_fast_nodes;
+	int32_t built_on_device;     /* 1 / 0                                                        */
+	int32_t reserved;
+} plu_build_stats;
+
+/* plu_gpu_upload_scene with the build location chosen (PLU_BUILD_*); stats may be NULL.
+ * plu_gpu_upload_scene(ctx, s) == plu_gpu_upload_scene_ex(ctx, s, PLU_BUILD_DEVICE, NULL).     */
+int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* scene, uint32_t build,
+                            plu_build_stats* stats);
+
+/* Copy a device table of the uploaded scene back (diagnostics and the build-parity tests).
+ * out may be NULL to query *n_bytes.                                                            */
+enum { PLU_TABLE_REF_NODES = 0, PLU_TABLE_PRIM_META = 1, PLU_TABLE_FAST_NODES = 2,
+       PLU_TABLE_FAST_INDEX = 3, PLU_TABLE_FAST_LEAF = 4 };
+int plu_gpu_download_table(plu_gpu_ctx* ctx, int which, void* out, int64_t cap_bytes, int64_t* n_bytes);
+
 /* renderer::render (renderer.cpp:98-150): out_rgb is target->_pixels, HOST, W*H*3 float,
  * row-major y down (texture.h:40-47), ACCUMULATED INTO (+=) like the reference.  Blocks.      */
 int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, float* out_rgb,

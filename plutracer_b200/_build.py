@@ -13,11 +13,11 @@ LIB_DIR = os.path.join(HERE, "_lib")
 LIB_PATH = os.path.join(LIB_DIR, "libplugpu.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["plugpu.cu", "host/scene_store.cpp", "host/bvh_build.cpp", "host/urn_loader.cpp"]
+SOURCES = ["plugpu.cu", "bvh_gpu.cu", "host/scene_store.cpp", "host/bvh_build.cpp", "host/urn_loader.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
-    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread", "-shared",
 ]
 
 

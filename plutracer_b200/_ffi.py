@@ -65,6 +65,16 @@ class RenderStats(C.Structure):
                 ("shade_vertices", C.c_uint64), ("shadow_entries", C.c_uint64), ("waves", C.c_uint64)]
 
 
+class BuildStats(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("ms_ref_order", C.c_double), ("ms_ref_nodes", C.c_double),
+                ("ms_fast_bvh", C.c_double), ("levels_ref", C.c_int32), ("levels_fast", C.c_int32),
+                ("host_tie_segments", C.c_int32), ("n_fast_nodes", C.c_int32), ("built_on_device", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+BUILD_DEVICE, BUILD_HOST = 0, 1
+TABLE_REF_NODES, TABLE_PRIM_META, TABLE_FAST_NODES, TABLE_FAST_INDEX, TABLE_FAST_LEAF = range(5)
+
 # every symbol include/plugpu.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 SYMBOLS = {
@@ -72,6 +82,8 @@ SYMBOLS = {
     "plu_gpu_destroy": (None, [_P]),
     "plu_gpu_last_error": (C.c_char_p, [_P]),
     "plu_gpu_upload_scene": (C.c_int, [_P, C.POINTER(SceneDesc)]),
+    "plu_gpu_upload_scene_ex": (C.c_int, [_P, C.POINTER(SceneDesc), C.c_uint32, C.POINTER(BuildStats)]),
+    "plu_gpu_download_table": (C.c_int, [_P, C.c_int, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "plu_gpu_render": (C.c_int, [_P, C.POINTER(RenderParams), _P, C.POINTER(RenderStats)]),
     "plu_gpu_render_device": (C.c_int, [_P, C.POINTER(RenderParams), _P, _P, C.POINTER(RenderStats)]),
     "plu_gpu_trace_primary": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P, _P]),

@@ -124,7 +124,7 @@ int32_t build_rec(build_ctx& c, size_t lo, size_t hi, int depth, box3& bounds, i
 		}
 		if (best_axis >= 0) {
 			float ext = cb.mx[best_axis] - cb.mn[best_axis], scale = 16.f / ext, base = cb.mn[best_axis];
-			auto it = std::partition(c.idx.begin() + (long)lo, c.idx.begin() + (long)hi, [&](int32_t s) {
+			auto it = std::stable_partition(c.idx.begin() + (long)lo, c.idx.begin() + (long)hi, [&](int32_t s) {
 				int k = std::min(15, std::max(0, (int)((c.cen[(size_t)s * 3 + best_axis] - base) * scale)));
 				return k < best_bin;
 			});
@@ -132,12 +132,9 @@ int32_t build_rec(build_ctx& c, size_t lo, size_t hi, int depth, box3& bounds, i
 			split_ok = mid > lo && mid < hi;
 		}
 	}
-	if (!split_ok) {   // equal centroids or depth guard: median split on the widest axis
-		int a = 0; for (int k = 1; k < 3; ++k) if (cb.mx[k] - cb.mn[k] > cb.mx[a] - cb.mn[a]) a = k;
-		mid = lo + n / 2;
-		std::nth_element(c.idx.begin() + (long)lo, c.idx.begin() + (long)mid, c.idx.begin() + (long)hi,
-		                 [&](int32_t x, int32_t y) { return c.cen[(size_t)x * 3 + a] < c.cen[(size_t)y * 3 + a]; });
-	}
+	// equal centroids or depth guard: halve in the current order (the partition above is stable, so the order — and with
+	// it every table — is the one bvh_gpu.cu's device build produces)
+	if (!split_ok) mid = lo + n / 2;
 	int32_t me = (int32_t)c.nodes->size();
 	c.nodes->emplace_back();
 	box3 b0, b1; int32_t n0, n1;

@@ -5,8 +5,10 @@
 #include "device/wavefront.cuh"
 #include "device/post.cuh"
 #include "host/bvh_build.h"
+#include "host/bvh_gpu.h"
 #include "host/scene_store.h"
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -108,25 +110,38 @@ static uint32_t blob_put(std::vector<unsigned char>& blob, const T* p, size_t n)
 	return (uint32_t)off;
 }
 
-extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
+static double wall_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) { return plu_gpu_upload_scene_ex(ctx, d, PLU_BUILD_DEVICE, nullptr); }
+
+extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
+	if (build != PLU_BUILD_DEVICE && build != PLU_BUILD_HOST) return fail(ctx, PLU_E_ARG, "build must be PLU_BUILD_DEVICE or PLU_BUILD_HOST");
 	std::string v = pluhost::validate_desc(d);
 	if (!v.empty()) return fail(ctx, PLU_E_ARG, v);
 	CU(cudaSetDevice(ctx->device));
 	free_scene(ctx);
 	size_t n = (size_t)d->n_prims;
+	const bool on_device = build == PLU_BUILD_DEVICE;
+	plu_build_stats bs; std::memset(&bs, 0, sizeof(bs));
+	double t_build = 0.0, t0 = wall_ms();
 
-	std::vector<int32_t> rank;
+	std::vector<int32_t> rank(n, 0);
 	if (d->prim_tie_rank) rank.assign(d->prim_tie_rank, d->prim_tie_rank + n);
-	else pluhost::reference_leaf_order(d, rank);
-	{   // the tie ranks must be a permutation
+	else if (!on_device) pluhost::reference_leaf_order(d, rank);
+	bs.ms_ref_order = wall_ms() - t0;
+	if (d->prim_tie_rank || !on_device) {   // the tie ranks must be a permutation
 		std::vector<char> seen(n, 0);
 		for (size_t i = 0; i < n; ++i) { if (rank[i] < 0 || (size_t)rank[i] >= n || seen[(size_t)rank[i]]) return fail(ctx, PLU_E_ARG, "prim_tie_rank is not a permutation"); seen[(size_t)rank[i]] = 1; }
 	}
 	std::vector<pluhost::ref_node_h> ref_nodes;
 	bool use_fast = d->n_prims > ctx->fast_threshold;
 	// the reference tree of a huge scene is only needed in verification mode; it is still built (O(n))
-	pluhost::build_ref_nodes(d, rank, ref_nodes);
+	t0 = wall_ms();
+	if (on_device) ref_nodes.assign(n ? 2 * n - 1 : 0, pluhost::ref_node_h{});   // written by the device build below
+	else pluhost::build_ref_nodes(d, rank, ref_nodes);
+	bs.ms_ref_nodes = wall_ms() - t0;
+	t_build = bs.ms_ref_order + bs.ms_ref_nodes;
 
 	std::vector<int32_t> meta(4 * n);
 	for (size_t s = 0; s < n; ++s) {
@@ -161,7 +176,21 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 		CU(cudaMalloc(&ctx->d_texels, bytes)); CU(cudaMemcpy(ctx->d_texels, d->image_texels, bytes, cudaMemcpyHostToDevice));
 	}
 	sc.tri_uv = ctx->d_tri_uv; sc.tri_normal = ctx->d_tri_normal; sc.texels = ctx->d_texels;
-	{
+	if (on_device) {
+		plubuild::device_tables tb;
+		tb.d_prim = (const float*)(ctx->d_blob + sc.off_prim);
+		tb.d_prim_meta = (int32_t*)(ctx->d_blob + sc.off_prim_meta);
+		tb.d_ref_nodes = ctx->d_blob + sc.off_ref_nodes;
+		std::string berr;
+		CU(cudaDeviceSynchronize());   // the table uploads above went through the default stream; the build runs on ctx->stream
+		t0 = wall_ms();
+		bool ok = plubuild::build_on_device(d, tb, ctx->stream, &bs, berr);
+		ctx->d_fast = (fast_node*)tb.d_fast; ctx->d_fast_index = tb.d_fast_index; ctx->d_fast_leaf = (float4*)tb.d_fast_leaf;
+		if (!ok) { free_scene(ctx); return fail(ctx, PLU_E_CUDA, "device BVH build: " + berr); }
+		sc.n_fast_nodes = n ? tb.n_fast_nodes : 0;
+		t_build = wall_ms() - t0;
+	} else {
+		t0 = wall_ms();
 		std::vector<pluhost::fast_node_h> fn; std::vector<int32_t> fi;
 		pluhost::build_fast_bvh(d, fn, fi);
 		if (!fn.empty()) {
@@ -191,7 +220,11 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 			CU(cudaMalloc(&ctx->d_fast_index, fi.size() * sizeof(int32_t))); CU(cudaMemcpy(ctx->d_fast_index, fi.data(), fi.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
 		}
 		sc.n_fast_nodes = (int32_t)fn.size();
+		bs.ms_fast_bvh = wall_ms() - t0; bs.n_fast_nodes = sc.n_fast_nodes;
+		t_build += bs.ms_fast_bvh;
 	}
+	bs.ms_total = t_build;
+	if (stats) *stats = bs;
 	sc.fast_nodes = use_fast ? ctx->d_fast : nullptr;
 	ctx->use_fast = use_fast;
 	ctx->has_specular = false;
@@ -199,7 +232,30 @@ extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) {
 	sc.fast_prim_index = ctx->d_fast_index; sc.fast_leaf = ctx->d_fast_leaf;
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
+	CU(cudaDeviceSynchronize());   // pageable uploads have landed before any stream renders from them
 	ctx->have_scene = true;
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_download_table(plu_gpu_ctx* ctx, int which, void* out, int64_t cap_bytes, int64_t* n_bytes) {
+	if (!ctx || !n_bytes) return PLU_E_ARG;
+	if (!ctx->have_scene) return fail(ctx, PLU_E_NOSCENE, "no scene uploaded");
+	CU(cudaSetDevice(ctx->device));
+	const scene_ref& sc = ctx->sc;
+	const void* src = nullptr; int64_t bytes = 0;
+	const bool fast = ctx->d_fast != nullptr;
+	switch (which) {
+	case PLU_TABLE_REF_NODES: src = ctx->d_blob + sc.off_ref_nodes; bytes = (int64_t)sc.n_ref_nodes * (int64_t)sizeof(ref_node); break;
+	case PLU_TABLE_PRIM_META: src = ctx->d_blob + sc.off_prim_meta; bytes = (int64_t)sc.n_prims * 16; break;
+	case PLU_TABLE_FAST_NODES: src = ctx->d_fast; bytes = fast ? (int64_t)sc.n_fast_nodes * (int64_t)sizeof(fast_node) : 0; break;
+	case PLU_TABLE_FAST_INDEX: src = ctx->d_fast_index; bytes = fast ? (int64_t)sc.n_prims * 4 : 0; break;
+	case PLU_TABLE_FAST_LEAF: src = ctx->d_fast_leaf; bytes = fast ? (int64_t)sc.n_prims * 48 : 0; break;
+	default: return fail(ctx, PLU_E_ARG, "unknown table");
+	}
+	*n_bytes = bytes;
+	if (!out || bytes == 0) return PLU_OK;
+	if (cap_bytes < bytes) return fail(ctx, PLU_E_ARG, "buffer too small for the table");
+	CU(cudaMemcpy(out, src, (size_t)bytes, cudaMemcpyDeviceToHost));
 	return PLU_OK;
 }
 

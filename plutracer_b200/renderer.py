@@ -35,9 +35,23 @@ class GpuContext:
         if rc != _ffi.PLU_OK:
             raise _ffi.PluError(rc, self._lib.plu_gpu_last_error(self._h).decode(errors="replace"))
 
-    def upload(self, scene):
-        self._check(self._lib.plu_gpu_upload_scene(self._h, scene.desc_ptr))
+    def upload(self, scene, build="device"):
+        """Copy the scene tables to the GPU and build both traversal structures there (build="device", the
+        default) or with the host restatement of the reference's builder (build="host").  Returns BuildStats."""
+        bs = _ffi.BuildStats()
+        where = {"device": _ffi.BUILD_DEVICE, "host": _ffi.BUILD_HOST}[build]
+        self._check(self._lib.plu_gpu_upload_scene_ex(self._h, scene.desc_ptr, where, C.byref(bs)))
         self._scene = scene
+        return bs
+
+    def download_table(self, which):
+        """Raw bytes (numpy uint8) of a device table of the uploaded scene: _ffi.TABLE_*."""
+        n = C.c_int64(0)
+        self._check(self._lib.plu_gpu_download_table(self._h, int(which), None, 0, C.byref(n)))
+        out = np.zeros(n.value, dtype=np.uint8)
+        if n.value:
+            self._check(self._lib.plu_gpu_download_table(self._h, int(which), out.ctypes.data, n.value, C.byref(n)))
+        return out
 
     @staticmethod
     def params(width, height, n_strata, seed=DEFAULT_SEED, flags=0, max_vertices=8, sample_begin=0, sample_stride=1,
