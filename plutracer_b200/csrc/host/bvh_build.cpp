@@ -35,17 +35,24 @@ box3 tight_bounds(const plu_scene_desc* d, int32_t s) {
 }
 float centroid(const box3& b, int axis) { return (b.mn[axis] + b.mx[axis]) * 1.f / 2.f; }   // aabb::center, cmmn.h:204-207
 
-void order_rec(const plu_scene_desc* d, std::vector<int32_t>& s, int axis, std::vector<int32_t>& dfs) {
+// (centre, id) pairs: the comparator reads the element itself instead of chasing two tables per comparison
+struct keyed { float k; int32_t v; };
+
+void order_rec(const std::vector<float>* cen, std::vector<int32_t>& s, int axis, std::vector<int32_t>& dfs) {
 	if (s.size() == 1) { dfs.push_back(s[0]); return; }
 	if (s.size() == 2) { dfs.push_back(s[0]); dfs.push_back(s[1]); return; }
-	// same std::sort, same comparator outcome as bvh_tree.cpp:23-27 => same permutation
-	std::sort(s.begin(), s.end(), [d, axis](int32_t a, int32_t b) {
-		return centroid(surface_bounds(d, a), axis) < centroid(surface_bounds(d, b), axis);
-	});
+	// same std::sort, same comparator outcomes on the same input order as bvh_tree.cpp:23-27 => same permutation
+	std::vector<keyed> kv(s.size());
+	for (size_t i = 0; i < s.size(); ++i) kv[i] = keyed{cen[axis][(size_t)s[i]], s[i]};
+	std::sort(kv.begin(), kv.end(), [](const keyed& a, const keyed& b) { return a.k < b.k; });
 	size_t mid = s.size() / 2;
-	std::vector<int32_t> lv(s.begin(), s.begin() + mid), rv(s.begin() + mid, s.end());
-	order_rec(d, lv, (axis + 1) % 3, dfs);
-	order_rec(d, rv, (axis + 1) % 3, dfs);
+	std::vector<int32_t> lv(mid), rv(s.size() - mid);
+	for (size_t i = 0; i < mid; ++i) lv[i] = kv[i].v;
+	for (size_t i = mid; i < s.size(); ++i) rv[i - mid] = kv[i].v;
+	std::vector<keyed>().swap(kv);
+	std::vector<int32_t>().swap(s);
+	order_rec(cen, lv, (axis + 1) % 3, dfs);
+	order_rec(cen, rv, (axis + 1) % 3, dfs);
 }
 
 box3 emit_ref(const plu_scene_desc* d, const std::vector<int32_t>& dfs, size_t lo, size_t hi, std::vector<ref_node_h>& out) {
@@ -159,7 +166,9 @@ void reference_leaf_order(const plu_scene_desc* d, std::vector<int32_t>& rank) {
 	std::vector<int32_t> s(n), dfs;
 	for (size_t i = 0; i < n; ++i) s[i] = (int32_t)i;   // load order (scene.h:268-297)
 	dfs.reserve(n);
-	order_rec(d, s, 0, dfs);
+	std::vector<float> cen[3];
+	for (int a = 0; a < 3; ++a) { cen[a].resize(n); for (size_t i = 0; i < n; ++i) cen[a][i] = centroid(surface_bounds(d, (int32_t)i), a); }
+	order_rec(cen, s, 0, dfs);
 	for (size_t k = 0; k < n; ++k) rank[(size_t)dfs[k]] = (int32_t)k;
 }
 

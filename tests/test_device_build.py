@@ -93,6 +93,18 @@ def test_equal_centres_are_decided_like_the_host_sort(gpu, n_side, dup):
         assert ds.host_tie_segments > 0
 
 
+def test_device_leaf_order_equals_the_reference_live_tree_on_ties(gpu):
+    """lattice.pluscene carries the ranks of the reference's own bvh_tree (equal centres everywhere): the device
+    build, given no ranks, must arrive at the same ones."""
+    sc = golden_scene("lattice")
+    ref_rank = np.ctypeslib.as_array(sc.desc.prim_tie_rank, shape=(sc.n_prims,)).copy()
+    bs = gpu.upload(_NoRank(sc), build="device")
+    meta = gpu.download_table(_ffi.TABLE_PRIM_META).view(np.int32).reshape(-1, 4)
+    assert bs.built_on_device == 1 and bs.host_tie_segments > 0
+    assert np.array_equal(meta[:, 3], ref_rank)
+    _assert_same_tables(gpu, sc, "lattice (ranks given)")
+
+
 def test_renders_through_both_builds_are_identical(gpu):
     from tools.gen_synth import make_scene
     sc = make_scene(5000, 7, "mixed", 96, 64, 2)

@@ -77,6 +77,26 @@ def test_leaf_order_matches_reference_tree(oracle, name):
     assert np.array_equal(sc.reference_leaf_order(), ref_rank)   # the product's own restatement of the build
 
 
+def test_leaf_order_with_equal_centres_matches_reference_tree(oracle):
+    """tests/golden/lattice.pluscene (make_lattice_golden.py): 1789 surfaces whose centres tie along every axis;
+    its ranks were dumped from the reference's live bvh_tree, i.e. they carry std::sort's order of equal elements."""
+    sc = golden_scene("lattice")
+    ref_rank = np.ctypeslib.as_array(sc.desc.prim_tie_rank, shape=(sc.n_prims,))
+    assert sorted(ref_rank.tolist()) == list(range(sc.n_prims))
+    assert np.array_equal(oracle.leaf_order(sc), ref_rank)
+    assert np.array_equal(sc.reference_leaf_order(), ref_rank)
+
+
+@pytest.mark.parametrize("n_side,dup", [(4, 1), (12, 1), (3, 40)])
+def test_leaf_order_with_equal_centres_oracle_vs_product(oracle, n_side, dup):
+    """Equal box centres in segments of more than 16 surfaces: the order is whatever std::sort's introsort leaves
+    (bvh_tree.cpp:23 is not a stable sort).  The oracle sorts surface ids through the comparator, the product
+    sorts (centre, id) pairs: same algorithm, same comparator outcomes, so the same permutation."""
+    from tests.test_device_build import _lattice
+    sc = _lattice(n_side, dup)
+    assert np.array_equal(oracle.leaf_order(sc), sc.reference_leaf_order())
+
+
 @pytest.mark.parametrize("name", ["refrac0", "room"])
 def test_philox_stream_converges_to_reference_renders(oracle, name):
     """Same path code, the Philox stream instead of mt19937: 1024 spp at 128x96 against the two
