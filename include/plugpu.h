@@ -140,8 +140,11 @@ enum { /* plu_render_params.flags                                               
 	PLU_RENDER_COUNT_BVH              = 1u << 2, /* fill bvh_nodes_visited / prims_tested         */
 	PLU_RENDER_BVH_FAST               = 1u << 3, /* use the tight SAH BVH even for a small scene
 	                                                (default: scenes with > 64 surfaces)         */
-	PLU_RENDER_PROFILE                = 1u << 4  /* CUDA events between all launches: fills
+	PLU_RENDER_PROFILE                = 1u << 4, /* CUDA events between all launches: fills
 	                                                ms_generate/extend/shade/connect/accumulate   */
+	PLU_RENDER_NO_LANE_REFILL         = 1u << 5  /* fast-BVH scenes: one ray per lane per iteration
+	                                                instead of persistent warps that refill idle
+	                                                lanes (A/B and parity of the two schedules)   */
 };
 
 typedef struct plu_render_params {

@@ -17,6 +17,7 @@ RENDER_BVH_REFERENCE = 2
 RENDER_COUNT_BVH = 4
 RENDER_BVH_FAST = 8
 RENDER_PROFILE = 16
+RENDER_NO_LANE_REFILL = 32
 POST_TONEMAP = 1
 
 

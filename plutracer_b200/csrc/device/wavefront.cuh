@@ -282,6 +282,92 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 	}
 }
 
+// ---- k_extend_pt ----------------------------------------------------------------------------------------------
+// k_extend for scenes that walk the fast BVH: persistent warps that REFILL finished lanes.  With one ray per lane
+// per iteration a warp runs as long as its longest ray (profiles/r01_summary.md: 10-13 of 32 threads active per
+// instruction on the 1M-surface scene, coherent camera rays included); here a lane whose walk ends waits only
+// until PT_REFILL lanes of its warp are idle, then those lanes retire their rays (extend_finish + queue push,
+// one 64-bit atomic per round) and take the next entries of the warp's chunk of the queue (PT_CHUNK entries per
+// atomic on the launch's work counter).  The walk state (fast_walker) lives across rounds.  Same per-ray
+// arithmetic as k_extend; only the order of the queue entries differs.
+#define CNT_WORK 24
+#define PT_CHUNK 128u
+#ifndef PT_REFILL
+#define PT_REFILL 12u
+#endif
+
+template <bool COUNT>
+__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce, uint32_t n_identity, uint32_t refill) {
+	constexpr uint32_t FULL = 0xffffffffu;
+	float4* const recs = wb.rec;
+	const bool ident = bounce == 0;
+	const uint32_t n = ident ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
+	const uint32_t* q = wb.queue[bounce & 1];
+	unsigned long long* cnt_pair = (unsigned long long*)(wb.counters + bounce * CNT_STRIDE + CNT_HIT_DIFFUSE);   // (diffuse, specular)
+	uint32_t* work = wb.counters + bounce * CNT_STRIDE + CNT_WORK;
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 0, (unsigned long long)n);
+	trace_counts tc; tc.nodes = 0; tc.prims = 0;
+	const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+	const float nl = (float)sc.n_lights;
+	const fast_node* nodes = sc.fast_nodes;
+	const float4* leaves = sc.fast_leaf;
+	fast_walker w; w.cur = fast_walker::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
+	int32_t stack[64];
+	bool have = false, exhausted = false;
+	uint32_t slot = 0; int flags = 0;
+	ray r; r.e = mk3(0.f); r.d = mk3(0.f);
+	uint32_t c_next = 0, c_end = 0;   // the warp's chunk of the queue (warp-uniform)
+	for (;;) {
+		// retire the lanes whose walk has ended
+		int cls = 0;
+		if (have && w.cur == fast_walker::DONE) {
+			cls = extend_finish(sc, recs, wb.rad, bounce, slot, r, flags, w.best >= 0, w.best_t, w.best, nl);
+			have = false;
+		}
+		const uint32_t md = __ballot_sync(FULL, cls == 1), ms = __ballot_sync(FULL, cls == 2);
+		if (md | ms) {
+			unsigned long long base = 0;
+			if (lane == 0) base = atomicAdd(cnt_pair, ((unsigned long long)__popc(ms) << 32) | (unsigned long long)__popc(md));
+			base = __shfl_sync(FULL, base, 0);
+			if (cls == 1) wb.q_hit[CLS_DIFFUSE][(uint32_t)base + __popc(md & lt)] = slot;
+			if (cls == 2) wb.q_hit[CLS_SPECULAR][(uint32_t)(base >> 32) + __popc(ms & lt)] = slot;
+		}
+		// refill: idle lanes take consecutive entries of the chunk; a second pass opens the next chunk at a chunk's end
+		for (int pass = 0; pass < 2 && !exhausted; ++pass) {
+			const uint32_t idle = __ballot_sync(FULL, !have);
+			if (!idle) break;
+			if (c_next == c_end) {
+				uint32_t b = 0;
+				if (lane == 0) b = atomicAdd(work, PT_CHUNK);
+				b = __shfl_sync(FULL, b, 0);
+				if (b >= n) { exhausted = true; break; }
+				c_next = b; c_end = min(b + PT_CHUNK, n);
+			}
+			const uint32_t idx = c_next + __popc(idle & lt);
+			if (!have && idx < c_end) {
+				slot = ident ? idx : q[idx];
+				float4 o = recs[4 * (size_t)slot], d = recs[4 * (size_t)slot + 1];
+				r.e = mk3(o); r.d = mk3(d); flags = __float_as_int(d.w);
+				w.begin(sc, r);
+				have = true;
+			}
+			c_next = min(c_next + (uint32_t)__popc(idle), c_end);
+		}
+		if (!__any_sync(FULL, have)) break;
+		// walk until fewer than min_active lanes are still walking (to the end once the queue is exhausted)
+		const uint32_t min_active = exhausted ? 1u : 33u - refill;
+		for (;;) {
+			w.round<COUNT>(nodes, leaves, r, stack, &tc);
+			if ((uint32_t)__popc(__ballot_sync(FULL, w.cur != fast_walker::DONE)) < min_active) break;
+		}
+	}
+	if (COUNT) {
+		unsigned long long a = tc.nodes, b = tc.prims;
+		for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(FULL, a, o); b += __shfl_down_sync(FULL, b, o); }
+		if (lane == 0) { atomicAdd(wb.stats + 2, a); atomicAdd(wb.stats + 3, b); }
+	}
+}
+
 // ---- k_shade --------------------------------------------------------------------------------------------------
 // One path vertex: everything renderer.cpp:66-83 does between two scene->hit calls, except the
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One

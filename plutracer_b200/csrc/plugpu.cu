@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -36,6 +37,7 @@ struct plu_gpu_ctx {
 	bool use_fast = false;
 	bool has_specular = false;     // any perfect-reflection / perfect-refraction / glass material
 	int32_t fast_threshold = 64;   // scenes with more surfaces than this use the fast BVH by default
+	uint32_t pt_refill = PT_REFILL; // k_extend_pt: idle lanes of a warp that trigger a retire + refill round
 	// wave buffers
 	uint32_t capacity = 0;         // path slots
 	wave_buffers wb{};
@@ -77,6 +79,7 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 		return PLU_E_CUDA;
 	}
 	ctx->sm_count = prop.multiProcessorCount;
+	if (const char* e = std::getenv("PLU_PT_REFILL")) { int v = std::atoi(e); if (v >= 1 && v <= 32) ctx->pt_refill = (uint32_t)v; }   // tuning knob
 	*out = ctx;
 	return PLU_OK;
 }
@@ -299,10 +302,11 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 }
 
 // dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
-struct launch_cfg { bool smem, count; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_shade[2], g_conn, g_acc; };
+struct launch_cfg { bool smem, count, no_pt; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_ext_pt, g_shade[2], g_conn, g_acc; };
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
-	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count;
+	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false;
+	c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
 	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
 	c.g_gen = grid_for(ctx, k_generate, 0);
@@ -359,7 +363,12 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
 			pf->mark(3, st);
 		} else {
-			if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
+			// fast BVH, no sphere (whose non-unit-direction rays need the reference tree): persistent warps with lane refill
+			const bool pt = sc.fast_nodes != nullptr && !sc.has_spheres && !c.no_pt;
+			if (pt) {
+				if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, w.n_slots, ctx->pt_refill);
+				else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, w.n_slots, ctx->pt_refill);
+			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
 			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
@@ -416,6 +425,7 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 	rc = ensure_wave(ctx, want);
 	if (rc != PLU_OK) return rc;
 	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
+	cfg.no_pt = (p->flags & PLU_RENDER_NO_LANE_REFILL) != 0;
 	CU(cudaMemsetAsync(ctx->wb.stats, 0, 8 * sizeof(unsigned long long), st));
 	CU(cudaEventRecord(ctx->ev0, st));
 	uint64_t launches = 0, samples = 0, waves = 0;

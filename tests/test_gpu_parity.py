@@ -189,3 +189,22 @@ def test_synth_paths_fast_equals_reference_tree_and_oracle(gpu, oracle, synth):
     assert np.nansum(a) > 0
     want = oracle.sample_radiance(synth, p_fast, first, 96, trig=0)
     assert same_bits(b[:96], want).all()
+
+
+def test_lane_refill_schedule_changes_nothing_but_the_order(gpu, synth):
+    """k_extend_pt (persistent warps that refill idle lanes, the default on fast-BVH scenes) against k_extend (one
+    ray per lane per iteration, PLU_RENDER_NO_LANE_REFILL): same image to the bit, same ray and vertex counts."""
+    from plutracer_b200 import GpuContext, _ffi
+    gpu.upload(synth)
+    w, h, n = 160, 120, 3
+    out = []
+    for flags in (FAST, FAST | _ffi.RENDER_NO_LANE_REFILL, FAST | _ffi.RENDER_COUNT_BVH, FAST | _ffi.RENDER_COUNT_BVH | _ffi.RENDER_NO_LANE_REFILL):
+        img = np.zeros((h, w, 3), np.float32)
+        st = gpu.render(GpuContext.params(w, h, n, seed=5, flags=flags, strata_per_wave=2), img)
+        out.append((img, st))
+    for img, st in out[1:]:
+        assert same_bits(out[0][0], img).all()
+        assert (st.samples, st.rays_extend, st.rays_shadow, st.shade_vertices, st.shadow_entries) == \
+               (out[0][1].samples, out[0][1].rays_extend, out[0][1].rays_shadow, out[0][1].shade_vertices, out[0][1].shadow_entries)
+    assert out[2][1].bvh_nodes_visited == out[3][1].bvh_nodes_visited > 0 and out[2][1].prims_tested == out[3][1].prims_tested > 0
+    assert np.nansum(out[0][0]) > 0

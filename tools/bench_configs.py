@@ -23,7 +23,7 @@ CONFIGS = [   # (scene, W, H, /smp)  — BASELINE.json configs[0..3], sizes from
 ]
 
 
-def run(ctx, sc, name, w, h, n, max_spp, steps=3):
+def run(ctx, sc, name, w, h, n, max_spp, steps=3, flags=0):
     import numpy as np
     import torch
     from plutracer_b200 import GpuContext, _ffi
@@ -31,14 +31,14 @@ def run(ctx, sc, name, w, h, n, max_spp, steps=3):
     ctx.upload(sc)
     fb = torch.zeros(h, w, 3, dtype=torch.float32, device="cuda")
     st_ = torch.cuda.current_stream().cuda_stream
-    p = GpuContext.params(w, h, n, seed=20261104, sample_begin=0, sample_stride=1, sample_count=spp)
+    p = GpuContext.params(w, h, n, seed=20261104, flags=flags, sample_begin=0, sample_stride=1, sample_count=spp)
     ctx.render_device(p, fb.data_ptr(), st_)
     best = None
     for _ in range(steps):
         fb.zero_()
         st = ctx.render_device(p, fb.data_ptr(), st_)
         best = st.ms_device if best is None else min(best, st.ms_device)
-    pp = GpuContext.params(w, h, n, seed=20261104, flags=_ffi.RENDER_PROFILE | _ffi.RENDER_COUNT_BVH, sample_begin=0, sample_stride=1, sample_count=min(spp, 16))
+    pp = GpuContext.params(w, h, n, seed=20261104, flags=flags | _ffi.RENDER_PROFILE | _ffi.RENDER_COUNT_BVH, sample_begin=0, sample_stride=1, sample_count=min(spp, 16))
     ps = ctx.render_device(pp, fb.data_ptr(), st_)
     rays = st.rays_extend + st.rays_shadow
     prays = max(ps.rays_extend + ps.rays_shadow, 1)
@@ -55,19 +55,21 @@ def main():
     ap.add_argument("--max-spp", type=int, default=256)
     ap.add_argument("--synth-n", type=int, default=1000000)
     ap.add_argument("--only", default="")
+    ap.add_argument("--no-refill", action="store_true", help="PLU_RENDER_NO_LANE_REFILL: the one-ray-per-lane schedule on fast-BVH scenes")
     a = ap.parse_args()
-    from plutracer_b200 import GpuContext, Scene
+    from plutracer_b200 import GpuContext, Scene, _ffi
     ctx = GpuContext(0)
+    flags = _ffi.RENDER_NO_LANE_REFILL if a.no_refill else 0
     for name, w, h, n in CONFIGS:
         if a.only and name not in a.only.split(","):
             continue
         sc = Scene.load_flat(os.path.join(ROOT, "tests", "golden", name + ".pluscene")).override(w, h, n)
-        print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp)), flush=True)
+        print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp, flags=flags)), flush=True)
     if a.synth_n > 0 and (not a.only or "synth" in a.only):
         from tools.gen_synth import make_scene
         for kind in ("boxes", "mixed"):
             sc = make_scene(a.synth_n, 1, kind, 1024, 1024, 8)
-            print(json.dumps(run(ctx, sc, f"synthetic {kind} n={sc.n_prims}", 1024, 1024, 8, a.max_spp)), flush=True)
+            print(json.dumps(run(ctx, sc, f"synthetic {kind} n={sc.n_prims}", 1024, 1024, 8, a.max_spp, flags=flags)), flush=True)
     ctx.close()
 
 
