@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--no-refill", action="store_true", help="PLU_RENDER_NO_LANE_REFILL: the one-ray-per-lane schedule on fast-BVH scenes")
     a = ap.parse_args()
     from plutracer_b200 import GpuContext, Scene, _ffi
+    from tools.gen_synth import make_scene
     ctx = GpuContext(0)
     flags = _ffi.RENDER_NO_LANE_REFILL if a.no_refill else 0
     for name, w, h, n in CONFIGS:
@@ -66,10 +67,26 @@ def main():
         sc = Scene.load_flat(os.path.join(ROOT, "tests", "golden", name + ".pluscene")).override(w, h, n)
         print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp, flags=flags)), flush=True)
     if a.synth_n > 0 and (not a.only or "synth" in a.only):
-        from tools.gen_synth import make_scene
         for kind in ("boxes", "mixed"):
             sc = make_scene(a.synth_n, 1, kind, 1024, 1024, 8)
             print(json.dumps(run(ctx, sc, f"synthetic {kind} n={sc.n_prims}", 1024, 1024, 8, a.max_spp, flags=flags)), flush=True)
+    if a.synth_n > 0 and a.only and "obj" in a.only.split(","):
+        # second flavour of config 5: the triangles as ONE triangle-mesh OBJ through the scene loader
+        import tempfile
+        import time
+        from tools.gen_synth import write_obj_scene
+        d = tempfile.mkdtemp(prefix="plu_synth_obj")
+        t0 = time.time(); urn = write_obj_scene(d, a.synth_n); t1 = time.time()
+        sc = Scene.load_urn(urn); t2 = time.time()
+        line = run(ctx, sc, f"synthetic triangle-mesh OBJ n={sc.n_prims}", 1024, 1024, 8, a.max_spp, flags=flags)
+        line["s_generate_obj"], line["s_load_urn_obj"] = round(t1 - t0, 2), round(t2 - t1, 2)
+        print(json.dumps(line), flush=True)
+    if a.synth_n > 0 and a.only and "spheres" in a.only.split(","):
+        # config 5 as SURVEY.md words it (spheres).  sphere::hit assumes unit directions and the reference feeds it
+        # non-unit ones, for which it "hits" spheres far off the ray: those rays must walk the reference's own tree
+        # (DESIGN.md 5.4), so this is the slow, exact mode — small image, few samples, bounded time.
+        sc = make_scene(a.synth_n, 1, "spheres", 256, 256, 8)
+        print(json.dumps(run(ctx, sc, f"synthetic spheres n={sc.n_prims}", 256, 256, 8, min(a.max_spp, 2), steps=1, flags=flags)), flush=True)
     ctx.close()
 
 

@@ -65,6 +65,11 @@ def make_tables(n, seed=1, kind="boxes"):
     data[:n, 0:3] = c - e
     data[:n, 4:7] = c + e
     uv = nr = None
+    if kind == "spheres":   # SURVEY.md 8(d) config 5 as written: a lattice of spheres (radius = the x half extent)
+        data[:n] = 0
+        data[:n, 0:3] = c
+        data[:n, 3] = e[:, 0]
+        tag[:n] = _ffi.PRIM_SPHERE
     if kind == "mixed":
         tri = rng.random(n) < 0.5
         k = int(tri.sum())
@@ -133,6 +138,42 @@ def write_urn(path, n, seed=1, width=1024, height=1024, n_strata=8):
         f.write("\t\tdiffuse-area-light [ box [0 70 0] [10 0.1 10] ] [50 50 50]\n\t]\n]\n")
 
 
+def write_obj_scene(directory, n, seed=1, width=1024, height=1024, n_strata=8):
+    """SURVEY.md 8(d) config 5, second flavour: n triangles as ONE triangle-mesh OBJ with full v/vt/vn corners
+    (scene.h:138-201) next to the floor box and the two lights; returns the path of the .urn.  Vertices are the
+    lattice triangles of kind=mixed (every cell a triangle), written with 9 significant digits."""
+    rng = np.random.default_rng(seed)
+    m = int(np.ceil(n ** (1.0 / 3.0)))
+    cell = 100.0 / m
+    idx = np.arange(n)
+    c = (np.stack([idx % m, (idx // m) % m, idx // (m * m)], 1) + 0.5) * cell - 50.0 + rng.uniform(-0.15, 0.15, (n, 3)) * cell
+    e = rng.uniform(0.15, 0.35, (n, 3)) * cell
+    v = (c[:, None, :] + rng.uniform(-1, 1, (n, 3, 3)) * e[:, None, :] * 1.5).astype(np.float32)
+    g = np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0])
+    g = (g / np.maximum(np.linalg.norm(g, axis=1, keepdims=True), 1e-20)).astype(np.float32)
+    os.makedirs(directory, exist_ok=True)
+    obj = os.path.join(directory, "synth_tri.obj")
+    with open(obj, "w") as f:
+        f.write("# tools/gen_synth.py write_obj_scene\nvt 0 0\nvt 1 0\nvt 0 1\n")
+        step = 50000
+        for b in range(0, n, step):
+            vv, gg = v[b:b + step].reshape(-1, 3), g[b:b + step]
+            f.write("".join("v %.9g %.9g %.9g\n" % tuple(r) for r in vv.tolist()))
+            f.write("".join("vn %.9g %.9g %.9g\n" % tuple(r) for r in gg.tolist()))
+        for b in range(0, n, step):
+            k = np.arange(b, min(b + step, n))
+            f.write("".join("f %d/1/%d %d/2/%d %d/3/%d\n" % (3 * i + 1, i + 1, 3 * i + 2, i + 1, 3 * i + 3, i + 1) for i in k.tolist()))
+    urn = os.path.join(directory, "synth_tri.urn")
+    with open(urn, "w") as f:
+        f.write(f"[\n\tresolution: [{width} {height}]\n\tantialiasing-samples: {n_strata}\n\tcamera: [ position: [0 0 -140] target: [0 0 0] up: [0 1 0] ]\n"
+                "\tmaterials: [\n\t\tfloor: [ diffuse [0.5 0.5 0.5] ]\n\t]\n\tobjects: [\n"
+                "\t\ttriangle-mesh \"synth_tri.obj\" [ diffuse [0.7 0.6 0.4] ]\n"
+                "\t\tbox [0 -52.1 0] [60 0.1 60] 'floor\n"
+                "\t\tpoint-light [0 80 0] [20000 20000 20000]\n"
+                "\t\tdiffuse-area-light [ box [0 70 0] [10 0.1 10] ] [50 50 50]\n\t]\n]\n")
+    return urn
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=1000000)
@@ -140,7 +181,10 @@ if __name__ == "__main__":
     ap.add_argument("--kind", default="boxes")
     ap.add_argument("--out", default="")
     ap.add_argument("--urn", default="")
+    ap.add_argument("--obj-dir", default="", help="write synth_tri.obj + synth_tri.urn (n triangles as one triangle-mesh) here")
     a = ap.parse_args()
+    if a.obj_dir:
+        print(write_obj_scene(a.obj_dir, a.n, a.seed))
     if a.urn:
         write_urn(a.urn, a.n, a.seed)
     if a.out:
