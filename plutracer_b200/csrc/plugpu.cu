@@ -44,6 +44,8 @@ struct plu_gpu_ctx {
 	void* d_wave_mem = nullptr;
 	float* d_fb = nullptr; size_t fb_floats = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	cudaStream_t aux = nullptr;                    // the specular shade kernel of a bounce runs beside the diffuse one
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 	int grid_generate = 0, grid_extend = 0, grid_shade = 0, grid_connect = 0;
 };
 
@@ -73,7 +75,10 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 	cudaDeviceProp prop;
 	if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
 	    (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-	    (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) {
+	    (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+	    (e = cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
 		g_create_error = std::string("CUDA context set-up failed: ") + cudaGetErrorString(e);
 		delete ctx;
 		return PLU_E_CUDA;
@@ -99,6 +104,9 @@ extern "C" void plu_gpu_destroy(plu_gpu_ctx* ctx) {
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	if (ctx->aux) cudaStreamDestroy(ctx->aux);
+	if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+	if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
 	delete ctx;
 }
 
@@ -302,10 +310,10 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 }
 
 // dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
-struct launch_cfg { bool smem, count, no_pt; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_ext_pt, g_shade[2], g_conn, g_acc; };
+struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_ext_pt, g_shade[2], g_conn, g_acc; };
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
-	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false;
+	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
 	c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
 	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
@@ -351,13 +359,22 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 	k_generate<<<c.g_gen, 256, 0, st>>>(sc, w, wb);
 	pf->mark(0, st);
 	int launches = 1;
+	// the two shade kernels of a bounce touch disjoint slots and push through atomics: the specular one (few vertices,
+	// mostly prologue and tail) runs on a second stream and fills the SMs the diffuse one leaves idle
+	const bool fork = ctx->has_specular && !pf->on && !c.no_fork;
 	for (int b = 0; b < w.max_vertices; ++b) {
 		if (c.smem) {
 			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
+			if (fork) cudaEventRecord(ctx->ev_fork, st);
 			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
-			if (ctx->has_specular) { k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b); launches++; }
+			if (ctx->has_specular) {
+				cudaStream_t s2 = fork ? ctx->aux : st;
+				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork, 0);
+				k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
+				if (fork) { cudaEventRecord(ctx->ev_join, s2); cudaStreamWaitEvent(st, ctx->ev_join, 0); }
+			}
 			pf->mark(2, st);
 			if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
 			else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
@@ -371,8 +388,14 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
+			if (fork) cudaEventRecord(ctx->ev_fork, st);
 			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
-			if (ctx->has_specular) { k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b); launches++; }
+			if (ctx->has_specular) {
+				cudaStream_t s2 = fork ? ctx->aux : st;
+				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork, 0);
+				k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
+				if (fork) { cudaEventRecord(ctx->ev_join, s2); cudaStreamWaitEvent(st, ctx->ev_join, 0); }
+			}
 			pf->mark(2, st);
 			if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
 			else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
