@@ -22,6 +22,8 @@ static_assert(sizeof(pluhost::fast_node_h) == sizeof(fast_node), "fast node layo
 
 static thread_local std::string g_create_error;
 
+#define PLU_PIPES 4
+
 struct plu_gpu_ctx {
 	int device = 0;
 	int sm_count = 0;
@@ -39,13 +41,17 @@ struct plu_gpu_ctx {
 	int32_t fast_threshold = 64;   // scenes with more surfaces than this use the fast BVH by default
 	uint32_t pt_refill = PT_REFILL; // k_extend_pt: idle lanes of a warp that trigger a retire + refill round
 	// wave buffers
-	uint32_t capacity = 0;         // path slots
-	wave_buffers wb{};
-	void* d_wave_mem = nullptr;
+	// wave buffers: two sets, so that two waves can be in flight on two streams (render_device)
+	uint32_t cap[PLU_PIPES] = {};      // path slots
+	wave_buffers wbs[PLU_PIPES] = {};
+	void* d_wave[PLU_PIPES] = {};
+	int n_pipes = 2;
 	float* d_fb = nullptr; size_t fb_floats = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-	cudaStream_t aux = nullptr;                    // the specular shade kernel of a bounce runs beside the diffuse one
-	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	cudaStream_t pipe[PLU_PIPES] = {};             // wave i of a render runs on pipe[i % n_pipes]; pipe[0] is unused (= the caller's stream)
+	cudaStream_t aux[PLU_PIPES] = {};              // per pipe: the specular shade kernel of a bounce runs beside the diffuse one
+	cudaEvent_t ev_fork[PLU_PIPES] = {}, ev_join[PLU_PIPES] = {};
+	cudaEvent_t ev_acc[PLU_PIPES] = {}, ev_start = nullptr;   // framebuffer adds stay in wave order
 	int grid_generate = 0, grid_extend = 0, grid_shade = 0, grid_connect = 0;
 };
 
@@ -76,14 +82,24 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 	if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
 	    (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
 	    (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-	    (e = cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking)) != cudaSuccess ||
-	    (e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
-	    (e = cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
+	    (e = cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming)) != cudaSuccess) {
 		g_create_error = std::string("CUDA context set-up failed: ") + cudaGetErrorString(e);
 		delete ctx;
 		return PLU_E_CUDA;
 	}
+	for (int k = 0; k < PLU_PIPES; ++k) {
+		if ((k > 0 && (e = cudaStreamCreateWithFlags(&ctx->pipe[k], cudaStreamNonBlocking)) != cudaSuccess) ||
+		    (e = cudaStreamCreateWithFlags(&ctx->aux[k], cudaStreamNonBlocking)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->ev_fork[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->ev_acc[k], cudaEventDisableTiming)) != cudaSuccess) {
+			g_create_error = std::string("CUDA context set-up failed: ") + cudaGetErrorString(e);
+			plu_gpu_destroy(ctx);
+			return PLU_E_CUDA;
+		}
+	}
 	ctx->sm_count = prop.multiProcessorCount;
+	if (const char* e = std::getenv("PLU_PIPES")) { int v = std::atoi(e); if (v >= 1 && v <= PLU_PIPES) ctx->n_pipes = v; }   // tuning knob
 	if (const char* e = std::getenv("PLU_PT_REFILL")) { int v = std::atoi(e); if (v >= 1 && v <= 32) ctx->pt_refill = (uint32_t)v; }   // tuning knob
 	*out = ctx;
 	return PLU_OK;
@@ -100,13 +116,19 @@ extern "C" void plu_gpu_destroy(plu_gpu_ctx* ctx) {
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	free_scene(ctx);
-	cudaFree(ctx->d_wave_mem); cudaFree(ctx->d_fb);
+	for (int k = 0; k < PLU_PIPES; ++k) cudaFree(ctx->d_wave[k]);
+	cudaFree(ctx->d_fb);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
-	if (ctx->aux) cudaStreamDestroy(ctx->aux);
-	if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-	if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+	if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+	for (int k = 0; k < PLU_PIPES; ++k) {
+		if (ctx->pipe[k]) cudaStreamDestroy(ctx->pipe[k]);
+		if (ctx->aux[k]) cudaStreamDestroy(ctx->aux[k]);
+		if (ctx->ev_fork[k]) cudaEventDestroy(ctx->ev_fork[k]);
+		if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
+		if (ctx->ev_acc[k]) cudaEventDestroy(ctx->ev_acc[k]);
+	}
 	delete ctx;
 }
 
@@ -278,16 +300,16 @@ static void select_bvh(const plu_gpu_ctx* ctx, scene_ref& sc, uint32_t flags) {
 // ---- wave buffers ---------------------------------------------------------------------------------------------
 #define PLU_MAX_VERTICES_CAP 64
 
-static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
-	if (ctx->capacity >= slots && ctx->d_wave_mem) return PLU_OK;
-	CU(cudaFree(ctx->d_wave_mem)); ctx->d_wave_mem = nullptr; ctx->capacity = 0;
+static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
+	if (ctx->cap[P] >= slots && ctx->d_wave[P]) return PLU_OK;
+	CU(cudaFree(ctx->d_wave[P])); ctx->d_wave[P] = nullptr; ctx->cap[P] = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
 	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
-	CU(cudaMalloc(&ctx->d_wave_mem, bytes));
-	unsigned char* p = (unsigned char*)ctx->d_wave_mem;
+	CU(cudaMalloc(&ctx->d_wave[P], bytes));
+	unsigned char* p = (unsigned char*)ctx->d_wave[P];
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
-	wave_buffers& wb = ctx->wb;
+	wave_buffers& wb = ctx->wbs[P];
 	// 16-byte rows first so every array is 256-byte aligned
 	wb.rec = (float4*)take(N * 64); wb.rad = (float4*)take(N * 16);
 	wb.sh_p = (float4*)take(N * 16); wb.sh_w1 = (float4*)take(N * 16); wb.sh_c1 = (float4*)take(N * 16);
@@ -296,8 +318,8 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots) {
 	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
-	if ((size_t)(p - (unsigned char*)ctx->d_wave_mem) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
-	ctx->capacity = slots;
+	if ((size_t)(p - (unsigned char*)ctx->d_wave[P]) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
+	ctx->cap[P] = slots;
 	return PLU_OK;
 }
 
@@ -351,8 +373,8 @@ struct wave_profiler {
 };
 
 // Enqueue one wave (generate -> [extend, shade, connect] x max_vertices); returns the launch count.
-static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& w, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr) {
-	wave_buffers& wb = ctx->wb;
+static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& w, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr, int P = 0) {
+	wave_buffers& wb = ctx->wbs[P];
 	wave_profiler none; if (!pf) pf = &none;
 	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);
 	pf->mark(-1, st);
@@ -367,13 +389,13 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			if (fork) cudaEventRecord(ctx->ev_fork, st);
+			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
 			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
 			if (ctx->has_specular) {
-				cudaStream_t s2 = fork ? ctx->aux : st;
-				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork, 0);
+				cudaStream_t s2 = fork ? ctx->aux[P] : st;
+				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
 				k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
-				if (fork) { cudaEventRecord(ctx->ev_join, s2); cudaStreamWaitEvent(st, ctx->ev_join, 0); }
+				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
 			}
 			pf->mark(2, st);
 			if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
@@ -388,13 +410,13 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
 			pf->mark(1, st);
-			if (fork) cudaEventRecord(ctx->ev_fork, st);
+			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
 			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
 			if (ctx->has_specular) {
-				cudaStream_t s2 = fork ? ctx->aux : st;
-				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork, 0);
+				cudaStream_t s2 = fork ? ctx->aux[P] : st;
+				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
 				k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
-				if (fork) { cudaEventRecord(ctx->ev_join, s2); cudaStreamWaitEvent(st, ctx->ev_join, 0); }
+				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
 			}
 			pf->mark(2, st);
 			if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
@@ -449,21 +471,35 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 	if (rc != PLU_OK) return rc;
 	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
 	cfg.no_pt = (p->flags & PLU_RENDER_NO_LANE_REFILL) != 0;
-	CU(cudaMemsetAsync(ctx->wb.stats, 0, 8 * sizeof(unsigned long long), st));
-	CU(cudaEventRecord(ctx->ev0, st));
-	uint64_t launches = 0, samples = 0, waves = 0;
 	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
+	// Two waves in flight: even waves on the caller's stream, odd waves on ctx->pipe1 with the second buffer set.
+	// Every kernel of a wave is a full-occupancy persistent grid whose CTAs end at different times; with two
+	// independent waves the SMs one wave's kernel leaves idle at its tail (and between its launches) run the other
+	// wave's kernels.  The framebuffer adds stay in wave order (k_accumulate waits for its predecessor's event),
+	// so the image does not depend on the overlap.
+	const int64_t waves_total = ((wh + ctx->cap[0] - 1) / ctx->cap[0]) * ((count + std::max<int64_t>(1, ctx->cap[0] / std::min<int64_t>(wh, ctx->cap[0])) - 1) / std::max<int64_t>(1, ctx->cap[0] / std::min<int64_t>(wh, ctx->cap[0])));
+	const int NP = (prof.on || waves_total < 2) ? 1 : (int)std::min<int64_t>(ctx->n_pipes, waves_total);
+	const bool two = NP > 1;
+	for (int k = 1; k < NP; ++k) { rc = ensure_wave(ctx, ctx->cap[0], k); if (rc != PLU_OK) return rc; }
+	for (int k = 0; k < NP; ++k) CU(cudaMemsetAsync(ctx->wbs[k].stats, 0, 8 * sizeof(unsigned long long), st));
+	CU(cudaEventRecord(ctx->ev0, st));
+	if (two) { CU(cudaEventRecord(ctx->ev_start, st)); for (int k = 1; k < NP; ++k) CU(cudaStreamWaitEvent(ctx->pipe[k], ctx->ev_start, 0)); }
+	uint64_t launches = 0, samples = 0, waves = 0;
 	// main image, then (compat) the overflow-column strip: sampler.h:74-78 renders x == W for rows 0..H-1
 	for (int pass = 0; pass < ((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? 2 : 1); ++pass) {
 		int64_t pbeg = pass == 0 ? 0 : wh, pend = pass == 0 ? wh : wh + p->height - 1;
 		for (int64_t p0 = pbeg; p0 < pend;) {
-			int64_t np = std::min<int64_t>(pend - p0, ctx->capacity);
-			int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->capacity / np));
+			int64_t np = std::min<int64_t>(pend - p0, ctx->cap[0]);
+			int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->cap[0] / np));
 			for (int32_t k0 = 0; k0 < count; k0 += K) {
 				w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
 				w.n_slots = (uint32_t)(np * w.kcount);
-				launches += (uint64_t)enqueue_wave(ctx, sc, w, cfg, st, &prof);
-				k_accumulate<<<cfg.g_acc, 256, 0, st>>>(w, ctx->wb, d_rgb, smp_wgt);
+				const int P = (int)(waves % (uint64_t)NP);
+				cudaStream_t sp = P ? ctx->pipe[P] : st;
+				launches += (uint64_t)enqueue_wave(ctx, sc, w, cfg, sp, &prof, P);
+				if (two && waves > 0) CU(cudaStreamWaitEvent(sp, ctx->ev_acc[(P + NP - 1) % NP], 0));   // the previous wave's add
+				k_accumulate<<<cfg.g_acc, 256, 0, sp>>>(w, ctx->wbs[P], d_rgb, smp_wgt);
+				if (two) CU(cudaEventRecord(ctx->ev_acc[P], sp));
 				prof.mark(4, st); prof.collect(st);
 				launches++;
 				samples += w.n_slots; waves++;
@@ -471,13 +507,15 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 			p0 += np;
 		}
 	}
+	if (two && waves > 0 && ((waves - 1) % (uint64_t)NP) != 0) CU(cudaStreamWaitEvent(st, ctx->ev_acc[(waves - 1) % (uint64_t)NP], 0));   // the last add ran on another pipe
 	CU(cudaEventRecord(ctx->ev1, st));
 	CU(cudaGetLastError());
 	CU(cudaStreamSynchronize(st));
 	if (stats) {
 		std::memset(stats, 0, sizeof(*stats));
-		unsigned long long h[8];
-		CU(cudaMemcpy(h, ctx->wb.stats, sizeof(h), cudaMemcpyDeviceToHost));
+		unsigned long long h[8], h1[8];
+		CU(cudaMemcpy(h, ctx->wbs[0].stats, sizeof(h), cudaMemcpyDeviceToHost));
+		for (int q = 1; q < NP; ++q) { CU(cudaMemcpy(h1, ctx->wbs[q].stats, sizeof(h1), cudaMemcpyDeviceToHost)); for (int k = 0; k < 8; ++k) h[k] += h1[k]; }
 		float ms = 0.f; CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
 		stats->samples = samples; stats->rays_extend = h[0]; stats->rays_shadow = h[1];
 		stats->bvh_nodes_visited = h[2]; stats->prims_tested = h[3];
@@ -570,15 +608,15 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 	launch_cfg cfg = make_cfg(ctx, false);
 	std::vector<float4> host;
 	for (int64_t p0 = pixel_begin; p0 < pixel_begin + pixel_count;) {
-		int64_t np = std::min<int64_t>(pixel_begin + pixel_count - p0, ctx->capacity);
-		int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->capacity / np));
+		int64_t np = std::min<int64_t>(pixel_begin + pixel_count - p0, ctx->cap[0]);
+		int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->cap[0] / np));
 		for (int32_t k0 = 0; k0 < count; k0 += K) {
 			w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
 			w.n_slots = (uint32_t)(np * w.kcount);
 			enqueue_wave(ctx, sc, w, cfg, ctx->stream);
 			CU(cudaGetLastError());
 			host.resize(w.n_slots);
-			CU(cudaMemcpyAsync(host.data(), ctx->wb.rad, (size_t)w.n_slots * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(host.data(), ctx->wbs[0].rad, (size_t)w.n_slots * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
 			CU(cudaStreamSynchronize(ctx->stream));
 			for (int32_t k = 0; k < w.kcount; ++k)
 				for (int64_t q = 0; q < np; ++q) {
