@@ -308,7 +308,9 @@ def main():
                     "ms_by_kernel": {"k_generate": ps.ms_generate, **ms, "k_accumulate": ps.ms_accumulate},
                     "algorithmic_bytes_per_sample": bytes_per_sample, "b_bvh_per_ray": b_bvh,
                     "whole_path_achieved_gbs": bytes_per_sample * value / world * 1e6 / 1e9,   # per GPU
-                    "whole_path_frac": bytes_per_sample * value / world * 1e6 / 1e9 / peak}
+                    "whole_path_frac": bytes_per_sample * value / world * 1e6 / 1e9 / peak,
+                    "note": "kernel durations come from a serial profiled pass (one event per launch); the timed steps keep two "
+                            "waves in flight on two streams, so `value` is higher than the sum of these durations implies"}
         cpu = None if (args.no_cpu_baseline or world > 1) else cpu_arm(4)
         line = {"metric": "Msamples/s on cornell-box.urn at 1024x1024, 4096 spp", "value": value, "unit": "Msamples/s", "n_gpus": world,
                 "steps": args.steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
