@@ -45,7 +45,7 @@ struct plu_gpu_ctx {
 	uint32_t cap[PLU_PIPES] = {};      // path slots
 	wave_buffers wbs[PLU_PIPES] = {};
 	void* d_wave[PLU_PIPES] = {};
-	int n_pipes = 2;
+	int n_pipes = 4;                   // waves in flight (PLU_PIPES=1..4 overrides); 2 suffice for cornell-box, launch-bound scenes gain up to 4
 	float* d_fb = nullptr; size_t fb_floats = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	cudaStream_t pipe[PLU_PIPES] = {};             // wave i of a render runs on pipe[i % n_pipes]; pipe[0] is unused (= the caller's stream)
