@@ -208,3 +208,30 @@ def test_lane_refill_schedule_changes_nothing_but_the_order(gpu, synth):
                (out[0][1].samples, out[0][1].rays_extend, out[0][1].rays_shadow, out[0][1].shade_vertices, out[0][1].shadow_entries)
     assert out[2][1].bvh_nodes_visited == out[3][1].bvh_nodes_visited > 0 and out[2][1].prims_tested == out[3][1].prims_tested > 0
     assert np.nansum(out[0][0]) > 0
+
+
+@pytest.mark.parametrize("name", ["cornell-box", "glass0"])
+def test_waves_in_flight_do_not_change_the_image(lib, name, monkeypatch):
+    """plu_gpu_render_device keeps up to four waves in flight on four streams (and the specular shade kernel on a
+    side stream); the framebuffer adds are chained in wave order, so the image must equal the serial schedule
+    (PLU_PIPES=1, PLU_NO_FORK) bit for bit — including the accumulation into a non-zero target."""
+    from plutracer_b200 import GpuContext
+    sc = golden_scene(name, 64, 48, 4)
+    imgs = []
+    for pipes, no_fork in (("4", False), ("1", True), ("3", False)):
+        monkeypatch.setenv("PLU_PIPES", pipes)
+        if no_fork:
+            monkeypatch.setenv("PLU_NO_FORK", "1")
+        else:
+            monkeypatch.delenv("PLU_NO_FORK", raising=False)
+        ctx = GpuContext(0)
+        try:
+            ctx.upload(sc)
+            img = np.full((48, 64, 3), 0.25, np.float32)
+            st = ctx.render(GpuContext.params(64, 48, 4, seed=3, strata_per_wave=1), img)   # 16 waves
+            assert st.waves == 16
+            imgs.append(img)
+        finally:
+            ctx.close()
+    assert same_bits(imgs[0], imgs[1]).all() and same_bits(imgs[0], imgs[2]).all()
+    assert np.nansum(imgs[0]) > 0.25 * imgs[0].size

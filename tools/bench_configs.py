@@ -23,7 +23,7 @@ CONFIGS = [   # (scene, W, H, /smp)  — BASELINE.json configs[0..3], sizes from
 ]
 
 
-def run(ctx, sc, name, w, h, n, max_spp, steps=3, flags=0):
+def run(ctx, sc, name, w, h, n, max_spp, steps=3, flags=0, spw=0):
     import numpy as np
     import torch
     from plutracer_b200 import GpuContext, _ffi
@@ -31,7 +31,7 @@ def run(ctx, sc, name, w, h, n, max_spp, steps=3, flags=0):
     ctx.upload(sc)
     fb = torch.zeros(h, w, 3, dtype=torch.float32, device="cuda")
     st_ = torch.cuda.current_stream().cuda_stream
-    p = GpuContext.params(w, h, n, seed=20261104, flags=flags, sample_begin=0, sample_stride=1, sample_count=spp)
+    p = GpuContext.params(w, h, n, seed=20261104, flags=flags, sample_begin=0, sample_stride=1, sample_count=spp, strata_per_wave=spw)
     ctx.render_device(p, fb.data_ptr(), st_)
     best = None
     for _ in range(steps):
@@ -55,6 +55,7 @@ def main():
     ap.add_argument("--max-spp", type=int, default=256)
     ap.add_argument("--synth-n", type=int, default=1000000)
     ap.add_argument("--only", default="")
+    ap.add_argument("--strata-per-wave", type=int, default=0, help="paths in flight per wave = W*H*this (0: library default, 2^22 paths)")
     ap.add_argument("--no-refill", action="store_true", help="PLU_RENDER_NO_LANE_REFILL: the one-ray-per-lane schedule on fast-BVH scenes")
     a = ap.parse_args()
     from plutracer_b200 import GpuContext, Scene, _ffi
@@ -65,7 +66,7 @@ def main():
         if a.only and name not in a.only.split(","):
             continue
         sc = Scene.load_flat(os.path.join(ROOT, "tests", "golden", name + ".pluscene")).override(w, h, n)
-        print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp, flags=flags)), flush=True)
+        print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp, flags=flags, spw=a.strata_per_wave)), flush=True)
     if a.synth_n > 0 and (not a.only or "synth" in a.only):
         for kind in ("boxes", "mixed"):
             sc = make_scene(a.synth_n, 1, kind, 1024, 1024, 8)
