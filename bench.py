@@ -301,16 +301,20 @@ def main():
         n_dom = int(ps.waves) * 8 * (2 if dom == "k_shade" else 1)   # launches of that kernel class in the profiled pass
         achieved = alg[dom] / (ms[dom] * 1e-3) / 1e9 if ms[dom] > 0 else 0.0
         bytes_per_sample = (alg["k_extend"] + alg["k_shade"] + alg["k_connect"]) / max(ps.samples, 1) + 12.0
+        # the scene of this workload is staged in shared memory: its BVH bytes never touch HBM, so the whole-path HBM
+        # figure leaves them out (the SURVEY.md 8d formula, which counts them, is reported beside it)
+        hbm_per_sample = (ps.rays_extend * 48.0 + alg["k_shade"] + ps.rays_shadow * 48.0) / max(ps.samples, 1) + 12.0
         traffic, traffic_src = measured_traffic(dom)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                     "traffic_source": traffic_src, "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
                     "peak_source": peak_src, "launches_profiled": int(n_dom), "avg_launch_ms": ms[dom] / max(n_dom, 1),
                     "ms_by_kernel": {"k_generate": ps.ms_generate, **ms, "k_accumulate": ps.ms_accumulate},
-                    "algorithmic_bytes_per_sample": bytes_per_sample, "b_bvh_per_ray": b_bvh,
-                    "whole_path_achieved_gbs": bytes_per_sample * value / world * 1e6 / 1e9,   # per GPU
-                    "whole_path_frac": bytes_per_sample * value / world * 1e6 / 1e9 / peak,
-                    "note": "kernel durations come from a serial profiled pass (one event per launch); the timed steps keep two "
-                            "waves in flight on two streams, so `value` is higher than the sum of these durations implies"}
+                    "algorithmic_bytes_per_sample": hbm_per_sample, "b_bvh_per_ray_on_chip": b_bvh,
+                    "survey_formula_bytes_per_sample_incl_on_chip_bvh": bytes_per_sample,
+                    "whole_path_achieved_gbs": hbm_per_sample * value / world * 1e6 / 1e9,   # per GPU, HBM bytes only
+                    "whole_path_frac": hbm_per_sample * value / world * 1e6 / 1e9 / peak,
+                    "note": "kernel durations come from a serial profiled pass (one event per launch); the timed steps keep several "
+                            "waves in flight on separate streams, so `value` is higher than the sum of these durations implies"}
         cpu = None if (args.no_cpu_baseline or world > 1) else cpu_arm(4)
         line = {"metric": "Msamples/s on cornell-box.urn at 1024x1024, 4096 spp", "value": value, "unit": "Msamples/s", "n_gpus": world,
                 "steps": args.steps, "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",

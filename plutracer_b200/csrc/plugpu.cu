@@ -484,9 +484,10 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 	const int64_t wcap = want;   // paths per wave of THIS render (the buffers may be larger from an earlier one)
 	const int64_t k_per_wave = std::max<int64_t>(1, wcap / std::min<int64_t>(wh, wcap));
 	const int64_t waves_total = ((wh + wcap - 1) / wcap) * ((count + k_per_wave - 1) / k_per_wave);
-	const int NP = (prof.on || waves_total < 2) ? 1 : (int)std::min<int64_t>(ctx->n_pipes, waves_total);
+	int NP = (prof.on || waves_total < 2) ? 1 : (int)std::min<int64_t>(ctx->n_pipes, waves_total);
+	for (int k = 1; k < NP; ++k)
+		if (ensure_wave(ctx, want, k) != PLU_OK) { cudaGetLastError(); NP = k; break; }   // no memory for another set: fewer waves in flight
 	const bool two = NP > 1;
-	for (int k = 1; k < NP; ++k) { rc = ensure_wave(ctx, want, k); if (rc != PLU_OK) return rc; }
 	for (int k = 0; k < NP; ++k) CU(cudaMemsetAsync(ctx->wbs[k].stats, 0, 8 * sizeof(unsigned long long), st));
 	CU(cudaEventRecord(ctx->ev0, st));
 	if (two) { CU(cudaEventRecord(ctx->ev_start, st)); for (int k = 1; k < NP; ++k) CU(cudaStreamWaitEvent(ctx->pipe[k], ctx->ev_start, 0)); }
