@@ -44,4 +44,13 @@ g++ -std=gnu++14 -O2 -fpermissive -w \
     -include "$here/ref_prelude.h" \
     -I"$shim" -I"$ref/inc" -I"$ref/depd/glm" -I"$ref/src" \
     "$here/ref_post_driver.cpp" -o "$out/plu_ref_post" -lpthread
-echo "build_ref: built $out/plu_ref $out/plu_ref_post"
+# the drop-in proof: the same reference TU with plu::gpu_renderer (integration/plu_gpu_renderer.h), linked against libplugpu.so
+lib="$here/../plutracer_b200/_lib"
+if [ -f "$lib/libplugpu.so" ]; then
+  g++ -std=gnu++14 -O2 -fpermissive -w -DPLU_WITH_GPU \
+      -DPLU_REF_ROOT="\"$ref\"" \
+      -include "$here/ref_prelude.h" \
+      -I"$shim" -I"$ref/inc" -I"$ref/depd/glm" -I"$ref/src" -I"$here/../include" -I"$here/../plutracer_b200/csrc/host" \
+      "$here/ref_driver.cpp" -o "$out/plu_ref_gpu" -L"$lib" -lplugpu -Wl,-rpath,'$ORIGIN/../../plutracer_b200/_lib' -lpthread
+fi
+echo "build_ref: built $out/plu_ref $out/plu_ref_post $out/plu_ref_gpu"

@@ -49,7 +49,11 @@
 #undef protected
 #undef private
 
+// plu_ref (checker): the flat-scene store is compiled in.  plu_ref_gpu (-DPLU_WITH_GPU, the drop-in proof): the same
+// symbols and the plu_gpu_* entry points come from libplugpu.so instead.
+#ifndef PLU_WITH_GPU
 #include "../plutracer_b200/csrc/host/scene_store.cpp"
+#endif
 
 namespace {
 
@@ -225,6 +229,29 @@ int main(int argc, char** argv) {
 			double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
 			printf("{\"mode\": \"render-flat\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f, \"threads\": %u}\n",
 			       L.W, L.H, L.samples, (unsigned long long)L.W * L.H * L.samples * L.samples, ms, std::thread::hardware_concurrency());
+#ifdef PLU_WITH_GPU
+		} else if ((mode == "render-gpu" || mode == "render-gpu-flat") && (argc == 7 || argc == 8)) {
+			// THE DROP-IN: the reference's own process (its loader or its object graph, its live bvh_tree, its
+			// sampler and texture2d) with plu::gpu_renderer in place of plu::renderer (main.cpp:171,177), then
+			// optionally its post-process + BMP writer through the device path (main.cpp:183,209)
+			int W = atoi(argv[3]), H = atoi(argv[4]), smp = atoi(argv[5]);
+			loaded L; flat_loaded F;
+			const bool flat = mode == "render-gpu-flat";
+			if (flat) load_flat(F, scene_path, W, H, smp); else load(L, scene_path, W, H, smp);
+			const int w = flat ? F.W : (int)L.sc->resolution.x, h = flat ? F.H : (int)L.sc->resolution.y;
+			const int n = flat ? F.samples : (int)L.sc->samples;
+			auto tx = std::make_shared<plu::texture2d>(glm::uvec2(w, h));
+			plu::samplers::stratified_sampler sampler(tx->size, glm::uvec2((unsigned)n), true);
+			plu::gpu_renderer r(flat ? (plu::surface*)F.tree.get() : (plu::surface*)L.tree.get(), flat ? F.cam : L.sc->cam, glm::uvec2(32), &sampler,
+			                    flat ? F.lights : L.sc->lights);
+			auto t0 = std::chrono::high_resolution_clock::now();
+			r.render(tx);
+			auto t1 = std::chrono::high_resolution_clock::now();
+			write_all(argv[6], &tx->pixel(glm::uvec2(0, 0)), (size_t)w * h * 12);
+			if (argc == 8) { plu::gpu_postprocesser pp; pp.postprocess(tx); plu::gpu_write_bmp(tx, argv[7]); }
+			printf("{\"mode\": \"%s\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f}\n", mode.c_str(),
+			       w, h, n, (unsigned long long)w * h * n * n, std::chrono::duration<double, std::milli>(t1 - t0).count());
+#endif
 		} else if (mode == "render-st" && (argc == 8 || argc == 12 || argc == 13)) {
 			int W = atoi(argv[3]), H = atoi(argv[4]), smp = atoi(argv[5]);
 			unsigned long seed = strtoul(argv[6], nullptr, 10);
