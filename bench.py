@@ -93,9 +93,10 @@ def measured_traffic(kernel):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             e = json.load(f)[kernel]
-        return float(e["dram_bytes_per_launch"]), e.get("source", "profiles/traffic.json")
+        extra = {k: e[k] for k in ("issue_active_pct", "threads_per_instruction", "warps_active_pct", "dram_throughput_pct") if k in e}
+        return float(e["dram_bytes_per_launch"]), e.get("source", "profiles/traffic.json"), extra
     except Exception:
-        return None, None
+        return None, None, {}
 
 
 # ---- the reference's own CPU renderer (oracle/_ref/plu_ref = unmodified reference sources) -----------------
@@ -304,9 +305,9 @@ def main():
         # the scene of this workload is staged in shared memory: its BVH bytes never touch HBM, so the whole-path HBM
         # figure leaves them out (the SURVEY.md 8d formula, which counts them, is reported beside it)
         hbm_per_sample = (ps.rays_extend * 48.0 + alg["k_shade"] + ps.rays_shadow * 48.0) / max(ps.samples, 1) + 12.0
-        traffic, traffic_src = measured_traffic(dom)
+        traffic, traffic_src, ncu_extra = measured_traffic(dom)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                    "traffic_source": traffic_src, "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
+                    "traffic_source": traffic_src, "ncu": ncu_extra,   # issue-slot / lane / occupancy figures of the same capture "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
                     "peak_source": peak_src, "launches_profiled": int(n_dom), "avg_launch_ms": ms[dom] / max(n_dom, 1),
                     "ms_by_kernel": {"k_generate": ps.ms_generate, **ms, "k_accumulate": ps.ms_accumulate},
                     "algorithmic_bytes_per_sample": hbm_per_sample, "b_bvh_per_ray_on_chip": b_bvh,
