@@ -192,10 +192,11 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
+	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
+	if (blockIdx.x * PLU_CTA >= n) return;   // a CTA without a first entry has no work: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
 	float4* st_d = st_o + 2 * PLU_CTA;             // [2][PLU_CTA]
-	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	const uint32_t* q = wb.queue[bounce & 1];
 	uint32_t* cnt_diffuse = wb.counters + bounce * CNT_STRIDE + CNT_HIT_DIFFUSE;
 	uint32_t* cnt_specular = wb.counters + bounce * CNT_STRIDE + CNT_HIT_SPECULAR;
@@ -377,9 +378,10 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
+	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
+	if (blockIdx.x * PLU_CTA >= n) return;   // no work for this CTA: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st_rec = (float4*)stage_base;          // [2][4][PLU_CTA]: the four quarters of the path record
-	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
 	const uint32_t* q_in = wb.q_hit[CLS];
 	uint32_t* cnt_shadow = wb.counters + bounce * CNT_STRIDE + CNT_SHADOW;
@@ -583,9 +585,10 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
+	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
+	if (blockIdx.x * PLU_CTA >= n) return;   // no work for this CTA: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st = (float4*)stage_base;   // [2][5][PLU_CTA]: p, w1, c1, w2, c2
-	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
 	const float nl = (float)sc.n_lights;
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
