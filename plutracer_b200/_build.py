@@ -17,6 +17,7 @@ SOURCES = ["plugpu.cu", "bvh_gpu.cu", "host/scene_store.cpp", "host/bvh_build.cp
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--threads", "4",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+    *(["-DPLU_LEAF_SMALL=" + os.environ["PLU_LEAF_SMALL"]] if os.environ.get("PLU_LEAF_SMALL") else []),
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread", "-shared",
 ]
 

@@ -295,7 +295,7 @@ struct fseg { int32_t lo, hi, parent, info; };                        // info = 
 struct bnode { float f[12]; int32_t child[2]; int32_t count[2]; };     // builder layout == pluhost::fast_node_h
 struct fsplit { int32_t axis, bin, mid, pad; };                        // axis < 0: halve in current order
 
-__device__ __forceinline__ bool seg_interior(int32_t n, int32_t depth) { return !(n <= 2 || (n <= 4 && depth > 8)); }
+__device__ __forceinline__ bool seg_interior(int32_t n, int32_t depth) { return !(n <= PLU_LEAF_SMALL || (n <= 4 && depth > 8)); }
 __device__ __forceinline__ int bin_of(float c, float base, float scale) { int k = (int)((c - base) * scale); return min(FB_NB - 1, max(0, k)); }
 __device__ __forceinline__ float half_area(const box3& b) { float x = b.mx[0] - b.mn[0], y = b.mx[1] - b.mn[1], z = b.mx[2] - b.mn[2]; return x * y + y * z + z * x; }
 

@@ -102,7 +102,7 @@ int32_t build_rec(build_ctx& c, size_t lo, size_t hi, int depth, box3& bounds, i
 		for (int a = 0; a < 3; ++a) { float v = c.cen[(size_t)s * 3 + a]; cb.mn[a] = std::min(cb.mn[a], v); cb.mx[a] = std::max(cb.mx[a], v); }
 	}
 	size_t n = hi - lo;
-	if (n <= 2 || (n <= 4 && depth > 8)) { count = (int32_t)n; return ~(int32_t)lo; }
+	if (n <= PLU_LEAF_SMALL || (n <= 4 && depth > 8)) { count = (int32_t)n; return ~(int32_t)lo; }
 	size_t mid = lo;
 	bool split_ok = false;
 	if (depth < 40) {

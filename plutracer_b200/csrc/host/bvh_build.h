@@ -4,6 +4,12 @@
 #include <cstdint>
 #include <vector>
 
+// leaf rule of the fast BVH, shared by the host builder and bvh_gpu.cu: a segment of up to PLU_LEAF_SMALL surfaces is a
+// leaf anywhere, one of up to 4 below depth 8
+#ifndef PLU_LEAF_SMALL
+#define PLU_LEAF_SMALL 2
+#endif
+
 namespace pluhost {
 
 struct ref_node_h { float lo[3]; int32_t skip; float hi[3]; int32_t prim; };            // == plud::ref_node
