@@ -307,7 +307,8 @@ def main():
         hbm_per_sample = (ps.rays_extend * 48.0 + alg["k_shade"] + ps.rays_shadow * 48.0) / max(ps.samples, 1) + 12.0
         traffic, traffic_src, ncu_extra = measured_traffic(dom)
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                    "traffic_source": traffic_src, "ncu": ncu_extra,   # issue-slot / lane / occupancy figures of the same capture "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
+                    "traffic_source": traffic_src, "ncu": ncu_extra,   # issue-slot / lane / occupancy figures of the same capture
+                    "algorithmic_bytes_per_launch": alg[dom] / max(n_dom, 1),
                     "peak_source": peak_src, "launches_profiled": int(n_dom), "avg_launch_ms": ms[dom] / max(n_dom, 1),
                     "ms_by_kernel": {"k_generate": ps.ms_generate, **ms, "k_accumulate": ps.ms_accumulate},
                     "algorithmic_bytes_per_sample": hbm_per_sample, "b_bvh_per_ray_on_chip": b_bvh,
