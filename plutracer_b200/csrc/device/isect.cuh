@@ -275,14 +275,27 @@ PLU_DEV unsigned long long submul2(unsigned long long m, unsigned long long e, u
 PLU_DEV float fmin3f(float a, float b, float c) { float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 
+// Traversal stack of the fast walk: the lowest S levels live in shared memory (column threadIdx.x of an
+// [S][256] array: lanes at different depths still hit 32 different banks), deeper levels in the caller's local
+// array.  A local-only stack (S = 0) sends every push/pop through L1, where it competes with the node loads.
+#ifndef PLU_SSTK
+#define PLU_SSTK 0
+#endif
+#define PLU_WALK_CTA 256   // == PLU_CTA and k_trace_rays' block size
+template <int S> struct walk_stack {
+	int32_t* sm;        // &shared[0][threadIdx.x] (unused when S == 0)
+	int32_t loc[64];    // host/bvh_build.cpp bounds the tree depth to 60
+	PLU_DEV void push(int sp, int32_t v) { if (S > 0 && sp < S) sm[sp * PLU_WALK_CTA] = v; else loc[sp - S] = v; }
+	PLU_DEV int32_t pop(int sp) const { return (S > 0 && sp < S) ? sm[sp * PLU_WALK_CTA] : loc[sp - S]; }
+};
+
 // The walk as a resumable state machine: k_extend_pt (wavefront.cuh) keeps one per lane across refills, trace_fast
 // runs one to completion.  cur: >= 0 inner node, < 0 leaf reference, DONE when the stack is exhausted.
 struct fast_walker {
 	static constexpr int32_t DONE = (int32_t)0x80000000;
 	unsigned long long ex2, ey2, ez2, ix2, iy2, iz2;
 	float best_t; int32_t best, best_rank, cur; int sp;
-	// the stack itself (int32_t[64]: host/bvh_build.cpp bounds the tree depth to 60) is a separate local array of the
-	// caller, so that these scalars stay in registers
+	// the stack itself (walk_stack) is a separate object of the caller, so that these scalars stay in registers
 
 	PLU_DEV void begin(const scene_ref& sc, const ray& r) {
 		const float ix = 1.f / r.d.x, iy = 1.f / r.d.y, iz = 1.f / r.d.z;
@@ -292,8 +305,8 @@ struct fast_walker {
 		cur = sc.n_fast_nodes > 0 ? 0 : DONE;
 	}
 	// one inner node (cur >= 0): both children in one pass, nearer child first, the other on the stack
-	template <bool COUNT>
-	PLU_DEV void node_step(const fast_node* nodes, int32_t* stack, trace_counts* tc) {
+	template <bool COUNT, class STK>
+	PLU_DEV void node_step(const fast_node* nodes, STK& stack, trace_counts* tc) {
 		const fast_node* nd = nodes + cur;
 		float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c); int4 d = __ldg(&nd->d);
 		if (COUNT) tc->nodes++;
@@ -309,11 +322,11 @@ struct fast_walker {
 		bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull);
 		if (h0 && h1) {
 			bool first1 = n1 < n0;
-			stack[sp++] = first1 ? d.x : d.y;
+			stack.push(sp++, first1 ? d.x : d.y);
 			cur = first1 ? d.y : d.x;
 		} else if (h0) cur = d.x;
 		else if (h1) cur = d.y;
-		else cur = sp > 0 ? stack[--sp] : DONE;
+		else { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; }
 	}
 	// one leaf: its <= 4 surface records
 	template <bool COUNT>
@@ -334,25 +347,29 @@ struct fast_walker {
 	// One round of the "while-while" walk: descend to the next leaf, then test it.  (Postponing the leaf while the
 	// lane keeps descending to a second one — "speculative traversal" — was measured: 6 % more nodes, 14 % more
 	// surface tests through the stale best t, 3 % slower; profiles/r01_summary.md.)
-	template <bool COUNT>
-	PLU_DEV void round(const fast_node* nodes, const float4* leaves, const ray& r, int32_t* stack, trace_counts* tc) {
+	// any_hit: the caller only asks WHETHER a surface is hit (point-light visibility, renderer.cpp:17 with
+	// is_delta()): the first hit ends the walk.  Whether a hit exists does not depend on the visiting order, and
+	// distance culling only starts after a first hit, so the answer is the closest-hit walk's.
+	template <bool COUNT, class STK>
+	PLU_DEV void round(const fast_node* nodes, const float4* leaves, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
 		while (cur >= 0) node_step<COUNT>(nodes, stack, tc);
 		if (cur == DONE) return;
 		leaf_test<COUNT>(leaves, r, cur, tc);
-		cur = sp > 0 ? stack[--sp] : DONE;
+		if (sp > 0 && !(any_hit && best >= 0)) cur = stack.pop(--sp); else cur = DONE;
 	}
 };
 
-template <bool COUNT>
-PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc) {
+template <bool COUNT, int S>
+PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
 	const fast_node* nodes = sc.fast_nodes;
 	const float4* leaves = sc.fast_leaf;   // 3 x float4 per leaf slot, in leaf order (plugpu.cu: upload)
 	fast_walker w; w.begin(sc, r);
-	int32_t stack[64];
+	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
+	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
 	// "while-while" walk: every lane first descends to its next leaf, then the warp tests leaves together;
 	// with one if/else per step (r01f: 8.6 of 32 threads active per instruction) node and leaf work of
 	// different lanes alternated serially
-	while (w.cur != fast_walker::DONE) w.round<COUNT>(nodes, leaves, r, stack, tc);
+	while (w.cur != fast_walker::DONE) w.round<COUNT>(nodes, leaves, r, stack, tc, any_hit);
 	t_out = w.best_t; prim_out = w.best;
 	return w.best >= 0;
 }
@@ -362,8 +379,8 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 // which the quadratic accepts rays that miss the sphere's bounds — no geometric BVH can reproduce
 // that, so such rays take the reference's own tree whenever the scene has spheres.
 template <bool COUNT, bool SMEM>
-PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc) {
-	if (sc.fast_nodes != nullptr && (!sc.has_spheres || fabsf(dot(r.d, r.d) - 1.f) <= 1e-5f)) return trace_fast<COUNT>(sc, r, t, prim, tc);
+PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc, bool any_hit = false) {
+	if (sc.fast_nodes != nullptr && (!sc.has_spheres || fabsf(dot(r.d, r.d) - 1.f) <= 1e-5f)) return trace_fast<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
 	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT, SMEM>(sc, r, root_bound, t, prim, tc);
 	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);
 }

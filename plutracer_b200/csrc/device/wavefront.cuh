@@ -118,6 +118,9 @@ PLU_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memo
 template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 #define PLU_CTA 256
+#ifndef PLU_ANYHIT
+#define PLU_ANYHIT 0   // 1: point-light shadow rays on the fast BVH stop at their first hit (k_connect)
+#endif
 // staging bytes per kernel (two stages of per-thread rows), added to the scene blob in dynamic shared memory
 #define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)
 #define PLU_STAGE_SHADE_IN (2 * 4 * PLU_CTA * 16)
@@ -313,7 +316,8 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 	const fast_node* nodes = sc.fast_nodes;
 	const float4* leaves = sc.fast_leaf;
 	fast_walker w; w.cur = fast_walker::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
-	int32_t stack[64];
+	__shared__ int32_t s_stack[PLU_SSTK > 0 ? PLU_SSTK : 1][PLU_SSTK > 0 ? PLU_CTA : 1];
+	walk_stack<PLU_SSTK> stack; stack.sm = &s_stack[0][PLU_SSTK > 0 ? threadIdx.x : 0];
 	bool have = false, exhausted = false;
 	uint32_t slot = 0; int flags = 0;
 	ray r; r.e = mk3(0.f); r.d = mk3(0.f);
@@ -622,7 +626,12 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 				r.d = mk3(w1);
 				float t; int32_t prim;
 				rays++;
-				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
+#if PLU_ANYHIT
+				const bool any_hit = (fl & SH_DELTA) != 0;   // a point light is visible iff NOTHING is hit: the first hit decides
+#else
+				const bool any_hit = false;
+#endif
+				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc, any_hit);
 				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
 				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
 			}
