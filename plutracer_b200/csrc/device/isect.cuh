@@ -281,10 +281,13 @@ PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, 
 #ifndef PLU_SSTK
 #define PLU_SSTK 0
 #endif
+#ifndef PLU_WIDE_WALK
+#define PLU_WIDE_WALK 0   // 1: compile the four-child walk (node_step_wide); it runs when the scene was uploaded with PLU_WIDE=1
+#endif
 #define PLU_WALK_CTA 256   // == PLU_CTA and k_trace_rays' block size
 template <int S> struct walk_stack {
 	int32_t* sm;        // &shared[0][threadIdx.x] (unused when S == 0)
-	int32_t loc[64];    // host/bvh_build.cpp bounds the tree depth to 60
+	int32_t loc[96];    // host/bvh_build.cpp bounds the tree depth to 60 (wide walk: <= 3 pushes per two levels)
 	PLU_DEV void push(int sp, int32_t v) { if (S > 0 && sp < S) sm[sp * PLU_WALK_CTA] = v; else loc[sp - S] = v; }
 	PLU_DEV int32_t pop(int sp) const { return (S > 0 && sp < S) ? sm[sp * PLU_WALK_CTA] : loc[sp - S]; }
 };
@@ -328,6 +331,47 @@ struct fast_walker {
 		else if (h1) cur = d.y;
 		else { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; }
 	}
+	// both children of the pair (A, B) of a node against the ray: entry / exit distances
+	PLU_DEV void slab_pair(float lxa, float lxb, float lya, float lyb, float lza, float lzb, float hxa, float hxb, float hya, float hyb,
+	                       float hza, float hzb, float& na, float& fa, float& nb, float& fb) const {
+		float lx0, lx1, ly0, ly1, lz0, lz1, hx0, hx1, hy0, hy1, hz0, hz1;
+		upk2(submul2(pk2(lxa, lxb), ex2, ix2), lx0, lx1); upk2(submul2(pk2(lya, lyb), ey2, iy2), ly0, ly1);
+		upk2(submul2(pk2(lza, lzb), ez2, iz2), lz0, lz1); upk2(submul2(pk2(hxa, hxb), ex2, ix2), hx0, hx1);
+		upk2(submul2(pk2(hya, hyb), ey2, iy2), hy0, hy1); upk2(submul2(pk2(hza, hzb), ez2, iz2), hz0, hz1);
+		na = fmax3f(fminf(lx0, hx0), fminf(ly0, hy0), fminf(lz0, hz0)); fa = fmin3f(fmaxf(lx0, hx0), fmaxf(ly0, hy0), fmaxf(lz0, hz0));
+		nb = fmax3f(fminf(lx1, hx1), fminf(ly1, hy1), fminf(lz1, hz1)); fb = fmin3f(fmaxf(lx1, hx1), fmaxf(ly1, hy1), fmaxf(lz1, hz1));
+	}
+	// one wide node (cur >= 0): four slots in one pass, nearest first, the other hits on the stack farthest first.
+	// The boxes are the fast BVH's own (grandchild boxes), the tests and the culling rule are node_step's, so the
+	// set of leaves that can hold the closest hit is still always visited; only the visiting order differs.
+	template <bool COUNT, class STK>
+	PLU_DEV void node_step_wide(const wide_node* nodes, STK& stack, trace_counts* tc) {
+		const wide_node* nd = nodes + cur;
+		const float4 lx = __ldg(&nd->lox), ly = __ldg(&nd->loy), lz = __ldg(&nd->loz);
+		const float4 hx = __ldg(&nd->hix), hy = __ldg(&nd->hiy), hz = __ldg(&nd->hiz);
+		const int4 rf = __ldg(&nd->ref);
+		if (COUNT) tc->nodes++;
+		const float cull = best_t + fabsf(best_t) * 1e-5f;
+		float n0, f0, n1, f1, n2, f2, n3, f3;
+		slab_pair(lx.x, lx.y, ly.x, ly.y, lz.x, lz.y, hx.x, hx.y, hy.x, hy.y, hz.x, hz.y, n0, f0, n1, f1);
+		slab_pair(lx.z, lx.w, ly.z, ly.w, lz.z, lz.w, hx.z, hx.w, hy.z, hy.w, hz.z, hz.w, n2, f2, n3, f3);
+		const bool h0 = !(f0 < n0) && !(f0 < 0.f) && !(n0 > cull) && rf.x != PLU_WIDE_EMPTY;
+		const bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull) && rf.y != PLU_WIDE_EMPTY;
+		const bool h2 = !(f2 < n2) && !(f2 < 0.f) && !(n2 > cull) && rf.z != PLU_WIDE_EMPTY;
+		const bool h3 = !(f3 < n3) && !(f3 < 0.f) && !(n3 > cull) && rf.w != PLU_WIDE_EMPTY;
+		const int c = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+		if (c == 0) { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; return; }
+		// misses sort behind every hit (hit keys are finite or -inf; a NaN key can only come from a degenerate ray)
+		float k0 = h0 ? n0 : INFINITY, k1 = h1 ? n1 : INFINITY, k2 = h2 ? n2 : INFINITY, k3 = h3 ? n3 : INFINITY;
+		int32_t r0 = rf.x, r1 = rf.y, r2 = rf.z, r3 = rf.w;
+#define PLU_CSWAP(ka, ra, kb, rb) { const bool s_ = kb < ka; const float tk_ = s_ ? kb : ka; const int32_t tr_ = s_ ? rb : ra; kb = s_ ? ka : kb; rb = s_ ? ra : rb; ka = tk_; ra = tr_; }
+		PLU_CSWAP(k0, r0, k1, r1) PLU_CSWAP(k2, r2, k3, r3) PLU_CSWAP(k0, r0, k2, r2) PLU_CSWAP(k1, r1, k3, r3) PLU_CSWAP(k1, r1, k2, r2)
+#undef PLU_CSWAP
+		if (c > 3) stack.push(sp++, r3);
+		if (c > 2) stack.push(sp++, r2);
+		if (c > 1) stack.push(sp++, r1);
+		cur = r0;
+	}
 	// one leaf: its <= 4 surface records
 	template <bool COUNT>
 	PLU_DEV void leaf_test(const float4* leaves, const ray& r, int32_t ref, trace_counts* tc) {
@@ -351,8 +395,9 @@ struct fast_walker {
 	// is_delta()): the first hit ends the walk.  Whether a hit exists does not depend on the visiting order, and
 	// distance culling only starts after a first hit, so the answer is the closest-hit walk's.
 	template <bool COUNT, class STK>
-	PLU_DEV void round(const fast_node* nodes, const float4* leaves, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
-		while (cur >= 0) node_step<COUNT>(nodes, stack, tc);
+	PLU_DEV void round(const fast_node* nodes, const wide_node* wide, const float4* leaves, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
+		if (PLU_WIDE_WALK && wide != nullptr) { while (cur >= 0) node_step_wide<COUNT>(wide, stack, tc); }
+		else { while (cur >= 0) node_step<COUNT>(nodes, stack, tc); }
 		if (cur == DONE) return;
 		leaf_test<COUNT>(leaves, r, cur, tc);
 		if (sp > 0 && !(any_hit && best >= 0)) cur = stack.pop(--sp); else cur = DONE;
@@ -369,7 +414,8 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 	// "while-while" walk: every lane first descends to its next leaf, then the warp tests leaves together;
 	// with one if/else per step (r01f: 8.6 of 32 threads active per instruction) node and leaf work of
 	// different lanes alternated serially
-	while (w.cur != fast_walker::DONE) w.round<COUNT>(nodes, leaves, r, stack, tc, any_hit);
+	const wide_node* wide = sc.wide_nodes;
+	while (w.cur != fast_walker::DONE) w.round<COUNT>(nodes, wide, leaves, r, stack, tc, any_hit);
 	t_out = w.best_t; prim_out = w.best;
 	return w.best >= 0;
 }

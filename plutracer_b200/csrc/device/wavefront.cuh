@@ -314,6 +314,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 	const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
 	const float nl = (float)sc.n_lights;
 	const fast_node* nodes = sc.fast_nodes;
+	const wide_node* wide = sc.wide_nodes;
 	const float4* leaves = sc.fast_leaf;
 	fast_walker w; w.cur = fast_walker::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
 	__shared__ int32_t s_stack[PLU_SSTK > 0 ? PLU_SSTK : 1][PLU_SSTK > 0 ? PLU_CTA : 1];
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 		// walk until fewer than min_active lanes are still walking (to the end once the queue is exhausted)
 		const uint32_t min_active = exhausted ? 1u : 33u - refill;
 		for (;;) {
-			w.round<COUNT>(nodes, leaves, r, stack, &tc);
+			w.round<COUNT>(nodes, wide, leaves, r, stack, &tc);
 			if ((uint32_t)__popc(__ballot_sync(FULL, w.cur != fast_walker::DONE)) < min_active) break;
 		}
 	}

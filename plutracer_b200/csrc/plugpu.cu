@@ -35,6 +35,7 @@ struct plu_gpu_ctx {
 	unsigned char* d_blob = nullptr;
 	float *d_tri_uv = nullptr, *d_tri_normal = nullptr, *d_texels = nullptr;
 	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr; float4* d_fast_leaf = nullptr;
+	wide_node* d_wide = nullptr;   // PLU_WIDE=1: four-child nodes collapsed from d_fast (k_collapse_wide)
 	bool blob_in_smem = false;
 	bool use_fast = false;
 	bool has_specular = false;     // any perfect-reflection / perfect-refraction / glass material
@@ -108,6 +109,7 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 
 static void free_scene(plu_gpu_ctx* ctx) {
 	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
+	cudaFree(ctx->d_wide); ctx->d_wide = nullptr;
 	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index); cudaFree(ctx->d_fast_leaf); ctx->d_fast_leaf = nullptr;
 	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
 	ctx->have_scene = false;
@@ -147,6 +149,39 @@ static uint32_t blob_put(std::vector<unsigned char>& blob, const T* p, size_t n)
 static double wall_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) { return plu_gpu_upload_scene_ex(ctx, d, PLU_BUILD_DEVICE, nullptr); }
+
+// Four-child nodes from the two-child fast BVH (scene_dev.cuh: wide_node): node i <- the children of its children.
+__device__ inline void wide_take(const fast_node& B, int j, float* lo, float* hi) {
+	const float* a = &B.a.x; const float* b = &B.b.x; const float* c = &B.c.x;
+	lo[0] = a[j]; lo[1] = a[2 + j]; lo[2] = b[j]; hi[0] = b[2 + j]; hi[1] = c[j]; hi[2] = c[2 + j];
+}
+__global__ void k_collapse_wide(int32_t n, const fast_node* in, wide_node* out) {
+	const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const fast_node B = in[i];
+	float lo[4][3], hi[4][3]; int32_t ref[4];
+	for (int s = 0; s < 4; ++s) { ref[s] = PLU_WIDE_EMPTY; for (int k = 0; k < 3; ++k) { lo[s][k] = INFINITY; hi[s][k] = -INFINITY; } }
+	for (int j = 0; j < 2; ++j) {
+		const int32_t c = j ? B.d.y : B.d.x;
+		if (c >= 0) {
+			const fast_node C = in[c];
+			for (int k = 0; k < 2; ++k) {
+				const int32_t r = k ? C.d.y : C.d.x;
+				wide_take(C, k, lo[2 * j + k], hi[2 * j + k]);
+				ref[2 * j + k] = (r < 0 && ((~r) & 7) == 0) ? PLU_WIDE_EMPTY : r;   // a leaf without surfaces (k_root_leaf) is no child
+			}
+		} else {
+			wide_take(B, j, lo[2 * j], hi[2 * j]);
+			ref[2 * j] = ((~c) & 7) == 0 ? PLU_WIDE_EMPTY : c;
+		}
+	}
+	wide_node W;
+	W.lox = make_float4(lo[0][0], lo[1][0], lo[2][0], lo[3][0]); W.loy = make_float4(lo[0][1], lo[1][1], lo[2][1], lo[3][1]);
+	W.loz = make_float4(lo[0][2], lo[1][2], lo[2][2], lo[3][2]); W.hix = make_float4(hi[0][0], hi[1][0], hi[2][0], hi[3][0]);
+	W.hiy = make_float4(hi[0][1], hi[1][1], hi[2][1], hi[3][1]); W.hiz = make_float4(hi[0][2], hi[1][2], hi[2][2], hi[3][2]);
+	W.ref = make_int4(ref[0], ref[1], ref[2], ref[3]); W.pad = make_int4(0, 0, 0, 0);
+	out[i] = W;
+}
 
 extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
@@ -264,6 +299,14 @@ extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d
 	ctx->has_specular = false;
 	for (int32_t i = 0; i < d->n_materials; ++i) if (d->materials[i].tag >= PLU_MAT_PERFECT_REFLECTION && d->materials[i].tag <= PLU_MAT_GLASS) ctx->has_specular = true;
 	sc.fast_prim_index = ctx->d_fast_index; sc.fast_leaf = ctx->d_fast_leaf;
+	sc.wide_nodes = nullptr;
+	if (PLU_WIDE_WALK && ctx->d_fast != nullptr && sc.n_fast_nodes > 0 && std::getenv("PLU_WIDE") != nullptr && std::atoi(std::getenv("PLU_WIDE")) > 0) {
+		CU(cudaMalloc(&ctx->d_wide, (size_t)sc.n_fast_nodes * sizeof(wide_node)));
+		k_collapse_wide<<<(sc.n_fast_nodes + 255) / 256, 256, 0, ctx->stream>>>(sc.n_fast_nodes, ctx->d_fast, ctx->d_wide);
+		CU(cudaGetLastError());
+		CU(cudaStreamSynchronize(ctx->stream));
+		sc.wide_nodes = ctx->d_wide;
+	}
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
 	ctx->wave_hint = 0;
