@@ -361,8 +361,10 @@ struct fast_walker {
 		const bool h3 = !(f3 < n3) && !(f3 < 0.f) && !(n3 > cull) && rf.w != PLU_WIDE_EMPTY;
 		const int c = (int)h0 + (int)h1 + (int)h2 + (int)h3;
 		if (c == 0) { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; return; }
-		// misses sort behind every hit (hit keys are finite or -inf; a NaN key can only come from a degenerate ray)
-		float k0 = h0 ? n0 : INFINITY, k1 = h1 ? n1 : INFINITY, k2 = h2 ? n2 : INFINITY, k3 = h3 ? n3 : INFINITY;
+		// misses sort behind every hit
+		// (a NaN entry distance — zero or NaN direction — sorts first, so that no miss can slip in front of a hit)
+		float k0 = h0 ? (n0 == n0 ? n0 : -INFINITY) : INFINITY, k1 = h1 ? (n1 == n1 ? n1 : -INFINITY) : INFINITY;
+		float k2 = h2 ? (n2 == n2 ? n2 : -INFINITY) : INFINITY, k3 = h3 ? (n3 == n3 ? n3 : -INFINITY) : INFINITY;
 		int32_t r0 = rf.x, r1 = rf.y, r2 = rf.z, r3 = rf.w;
 #define PLU_CSWAP(ka, ra, kb, rb) { const bool s_ = kb < ka; const float tk_ = s_ ? kb : ka; const int32_t tr_ = s_ ? rb : ra; kb = s_ ? ka : kb; rb = s_ ? ra : rb; ka = tk_; ra = tr_; }
 		PLU_CSWAP(k0, r0, k1, r1) PLU_CSWAP(k2, r2, k3, r3) PLU_CSWAP(k0, r0, k2, r2) PLU_CSWAP(k1, r1, k3, r3) PLU_CSWAP(k1, r1, k2, r2)
