@@ -279,7 +279,7 @@ PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, 
 // [S][256] array: lanes at different depths still hit 32 different banks), deeper levels in the caller's local
 // array.  A local-only stack (S = 0) sends every push/pop through L1, where it competes with the node loads.
 #ifndef PLU_SSTK
-#define PLU_SSTK 0
+#define PLU_SSTK 8
 #endif
 #ifndef PLU_WIDE_WALK
 #define PLU_WIDE_WALK 0   // 1: compile the four-child walk (node_step_wide); it runs when the scene was uploaded with PLU_WIDE=1

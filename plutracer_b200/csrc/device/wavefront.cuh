@@ -119,7 +119,7 @@ template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_grou
 
 #define PLU_CTA 256
 #ifndef PLU_ANYHIT
-#define PLU_ANYHIT 0   // 1: point-light shadow rays on the fast BVH stop at their first hit (k_connect)
+#define PLU_ANYHIT 1   // 1: point-light shadow rays on the fast BVH stop at their first hit (k_connect)
 #endif
 // staging bytes per kernel (two stages of per-thread rows), added to the scene blob in dynamic shared memory
 #define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)

@@ -371,7 +371,9 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 template <class K>
 static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 	int occ = 0;
-	if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	cudaFuncAttributes fa; size_t fixed = 0;   // static shared memory (push counters, PLU_SSTK stack levels) counts towards the 48 KB default limit
+	if (cudaFuncGetAttributes(&fa, kernel) == cudaSuccess) fixed = fa.sharedSizeBytes;
+	if (smem + fixed > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, PLU_CTA, smem) != cudaSuccess || occ < 1) occ = 1;
 	return ctx->sm_count * occ;
 }
