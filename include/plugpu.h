@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define PLUGPU_ABI_VERSION 1
+#define PLUGPU_ABI_VERSION 2
 
 /* ---- error codes ------------------------------------------------------------------------- */
 enum {
@@ -155,7 +155,10 @@ typedef struct plu_render_params {
 	uint32_t flags;
 	int32_t  sample_begin;         /* this call renders sample indices                          */
 	int32_t  sample_stride;        /*   s = sample_begin + k*sample_stride, k < sample_count    */
-	int32_t  sample_count;         /*   (0 -> all n_strata^2: begin 0, stride 1)                */
+	int32_t  sample_count;         /*   (0 -> all n_strata^2: begin 0, stride 1).  Every s must
+	                                  be < n_strata^2 (else PLU_E_ARG); a subset is still
+	                                  weighted by 1/n_strata^2 per sample (renderer.cpp:100),
+	                                  so the parts of a split add up to the whole image         */
 	int32_t  strata_per_wave;      /* paths in flight = W*H*this; 0 -> library picks             */
 	int32_t  reserved;
 } plu_render_params;
@@ -176,12 +179,32 @@ typedef struct plu_render_stats {
 	uint64_t shade_vertices;       /* path vertices shaded (= extension rays that hit)          */
 	uint64_t shadow_entries;       /* shaded vertices that needed a connection                  */
 	uint64_t waves;                /* waves (batches of paths in flight) this call ran          */
+	/* ABI 2: multi-device contexts (plu_gpu_create_multi).  Counters above are sums over the
+	 * devices, ms_device is the slowest device's render time.                                  */
+	double   ms_reduce;            /* the NCCL reduce of the per-device framebuffers (0: one GPU) */
+	int32_t  n_devices;            /* devices that took part in this call                       */
+	int32_t  reserved;
 } plu_render_stats;
 
 typedef struct plu_gpu_ctx plu_gpu_ctx;
 
 /* Create a context on CUDA device `device` (one process / context per GPU).                     */
 int  plu_gpu_create(int device, plu_gpu_ctx** out);
+/* Create ONE context that drives `n_devices` GPUs of this box from a single process (SURVEY.md
+ * 8b/8e): the scene is deep-copied to every device; plu_gpu_render / plu_gpu_render_device give
+ * device g the samples k = g (mod n_devices) of the call's sample set (per-pixel stratification
+ * is kept, sampler.h:58-69; nothing is exchanged while rendering), one host thread per device
+ * enqueues its waves, and the per-device float framebuffers are combined by ONE
+ * ncclReduce(sum, float32, W*H*3, root = devices[0]) over NVLink on communicators the context
+ * owns (ncclCommInitAll; libnccl.so.2 is loaded at run time, only by this call).  All other
+ * entry points (parity hooks, post-process, table download) run on devices[0].  devices == NULL:
+ * the first n_devices visible devices; n_devices == 0 with devices == NULL: every visible one.
+ * n_devices == 1 is exactly plu_gpu_create(devices[0]).  The image is independent of the device
+ * count up to the float summation order of the reduce (Philox counters carry the global sample
+ * index).                                                                                        */
+int  plu_gpu_create_multi(const int* devices, int n_devices, plu_gpu_ctx** out);
+/* Number of devices the context drives (1 for plu_gpu_create).                                  */
+int  plu_gpu_device_count(const plu_gpu_ctx* ctx);
 void plu_gpu_destroy(plu_gpu_ctx* ctx);
 /* Message of the last failing call on ctx (ctx may be NULL: last plu_gpu_create failure).       */
 const char* plu_gpu_last_error(const plu_gpu_ctx* ctx);
@@ -227,9 +250,12 @@ int plu_gpu_download_table(plu_gpu_ctx* ctx, int which, void* out, int64_t cap_b
 int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, float* out_rgb,
                    plu_render_stats* stats);
 
-/* Same, but d_rgb is a DEVICE pointer on ctx's device and the work is enqueued on `stream`
- * (a cudaStream_t, NULL = the context's own stream) — used for multi-GPU so the per-GPU
- * framebuffers can be combined by one NCCL reduce.  Synchronises `stream` before returning.    */
+/* Same, but d_rgb is a DEVICE pointer on ctx's (first) device and the work is enqueued on
+ * `stream` (a cudaStream_t; NULL = stream 0, the legacy default stream, as everywhere in CUDA —
+ * so work the caller enqueued on stream 0, e.g. the framebuffer initialisation, is ordered
+ * before the render) — for callers that keep the framebuffer on the device (one process per
+ * GPU + their own reduce, or a device-side post-process).  Synchronises `stream` before
+ * returning.                                                                                   */
 int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb,
                           void* stream, plu_render_stats* stats);
 
@@ -264,9 +290,21 @@ int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t width, int32_t height, const fl
                        uint32_t flags, unsigned char* out_bmp, int64_t cap);
 /* Same from a DEVICE framebuffer (e.g. the one plu_gpu_render_device filled): tone map +
  * quantise + BMP layout in one kernel, only the bytes travel to the host (3 instead of 12 per
- * pixel).  Work is enqueued on `stream` (NULL = the context's) and synchronised.               */
+ * pixel).  Work is enqueued on `stream` (NULL = stream 0, the legacy default stream) and
+ * synchronised.                                                                                 */
 int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t width, int32_t height, const float* d_rgb,
                               uint32_t flags, void* stream, unsigned char* out_bmp, int64_t cap);
+
+/* The context keeps the image of its last plu_gpu_render on its (first) device.  These two run
+ * the steps after the path on that RESIDENT framebuffer, so the float pixels cross PCIe once
+ * (the render's own download) instead of once per step: tone map in place on the device
+ * (rgb_out, HOST, W*H*3 float, may be NULL: nothing is copied back), and the .bmp bytes
+ * (PLU_POST_TONEMAP fuses the tone map in front without modifying the resident image).
+ * PLU_E_NOSCENE when no render has left an image.  The caller vouches that the host copy has not
+ * been edited in between (the reference draws its watermark on the host between main.cpp:183 and
+ * :209 — use plu_gpu_encode_bmp for that flow).                                                 */
+int plu_gpu_postprocess_resident(plu_gpu_ctx* ctx, float* rgb_out);
+int plu_gpu_encode_bmp_resident(plu_gpu_ctx* ctx, uint32_t flags, unsigned char* out_bmp, int64_t cap);
 
 /* ---- host-side scene plumbing (no GPU needed) --------------------------------------------- */
 typedef struct plu_scene plu_scene;   /* owns the arrays a plu_scene_desc points at              */

@@ -15,8 +15,11 @@
 // (after all std + GLM headers) as oracle/ref_driver.cpp does.
 #pragma once
 #include "plugpu.h"
+#include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 namespace plu {
@@ -189,6 +192,34 @@ struct flattener {
 
 }  // namespace gpu
 
+namespace gpu {
+// ONE libplugpu context per process, created on first use and kept alive across render / postprocess / write_bmp
+// (CUDA set-up, the wave buffers and the device framebuffer are paid once, not per image).  Devices:
+//   PLU_DEVICES unset      every visible GPU of the box (plu_gpu_create_multi: samples split k = g (mod n), scene
+//                          replicated, ONE ncclReduce of the float framebuffers to the first device)
+//   PLU_DEVICES="0,2,5"    exactly these;  PLU_DEVICES="0": a single GPU (no NCCL is loaded)
+inline plu_gpu_ctx* shared_ctx() {
+	struct holder {
+		plu_gpu_ctx* c = nullptr;
+		~holder() { plu_gpu_destroy(c); }
+	};
+	static holder h;
+	if (h.c) return h.c;
+	std::vector<int> devs;
+	if (const char* e = std::getenv("PLU_DEVICES")) {
+		for (const char* p = e; *p;) {
+			char* end = nullptr; long v = std::strtol(p, &end, 10);
+			if (end == p) break;
+			devs.push_back((int)v);
+			p = (*end == ',') ? end + 1 : end;
+		}
+	}
+	int rc = devs.empty() ? plu_gpu_create_multi(nullptr, 0, &h.c) : plu_gpu_create_multi(devs.data(), (int)devs.size(), &h.c);
+	if (rc != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
+	return h.c;
+}
+}  // namespace gpu
+
 // Same constructor and render() signature as plu::renderer (renderer.h:20-25).
 struct gpu_renderer {
 	const uvec2 tile_size;  // kept for signature compatibility; the GPU path has no tiles
@@ -198,6 +229,7 @@ struct gpu_renderer {
 	sampler* main_sampler;
 	uint64_t seed = 20261104ull;
 	uint32_t flags = 0;
+	mutable plu_render_stats last_stats = {};
 
 	gpu_renderer(surface* S, const camera& C, uvec2 tile_size, sampler* smp, const vector<shared_ptr<light>>& l)
 		: tile_size(tile_size), scene(S), lights(l), cam(C), main_sampler(smp) {}
@@ -216,9 +248,7 @@ struct gpu_renderer {
 		gpu::flattener(fs).run(surfs, lights, cam);
 		plu_scene_desc d = fs.desc();
 
-		plu_gpu_ctx* ctx = nullptr;
-		if (plu_gpu_create(0, &ctx) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
-		struct guard { plu_gpu_ctx* c; ~guard() { plu_gpu_destroy(c); } } g{ctx};
+		plu_gpu_ctx* ctx = gpu::shared_ctx();
 		if (plu_gpu_upload_scene(ctx, &d) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
 		plu_render_params p = {};
 		p.width = (int32_t)target->size.x; p.height = (int32_t)target->size.y;
@@ -226,33 +256,46 @@ struct gpu_renderer {
 		p.max_vertices = 8; p.seed = seed; p.flags = flags;
 		// texture2d::_pixels is a packed vec3 array (texture.h:29); pixel(0,0) is its first float
 		float* rgb = &target->pixel(uvec2(0, 0)).x;
-		if (plu_gpu_render(ctx, &p, rgb, nullptr) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
+		if (plu_gpu_render(ctx, &p, rgb, &last_stats) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
 	}
 };
 
 // Drop-in for plu::postprocesser (main.cpp:76-112): same postprocess(shared_ptr<texture2d>) call.
 struct gpu_postprocesser {
 	void postprocess(shared_ptr<texture2d> rt) {
-		plu_gpu_ctx* ctx = nullptr;
-		if (plu_gpu_create(0, &ctx) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
-		struct guard { plu_gpu_ctx* c; ~guard() { plu_gpu_destroy(c); } } g{ctx};
+		plu_gpu_ctx* ctx = gpu::shared_ctx();
 		if (plu_gpu_postprocess(ctx, (int32_t)rt->size.x, (int32_t)rt->size.y, &rt->pixel(uvec2(0, 0)).x) != PLU_OK)
 			throw std::runtime_error(plu_gpu_last_error(ctx));
 	}
 };
 
-// texture2d::write_bmp(filename) (texture.cpp:178-194) with clamp / quantise / BMP layout on the device.
-inline void gpu_write_bmp(shared_ptr<texture2d> rt, const std::string& filename) {
-	plu_gpu_ctx* ctx = nullptr;
-	if (plu_gpu_create(0, &ctx) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
-	struct guard { plu_gpu_ctx* c; ~guard() { plu_gpu_destroy(c); } } g{ctx};
-	int64_t n = plu_bmp_size((int32_t)rt->size.x, (int32_t)rt->size.y);
-	std::vector<unsigned char> bytes((size_t)n);
-	if (plu_gpu_encode_bmp(ctx, (int32_t)rt->size.x, (int32_t)rt->size.y, &rt->pixel(uvec2(0, 0)).x, 0, bytes.data(), n) != PLU_OK)
-		throw std::runtime_error(plu_gpu_last_error(ctx));
+inline void gpu_write_file(const std::string& filename, const std::vector<unsigned char>& bytes) {
 	FILE* f = fopen(filename.c_str(), "wb");
 	if (!f) throw std::runtime_error("cannot open " + filename);
 	fwrite(bytes.data(), 1, bytes.size(), f);
 	fclose(f);
+}
+
+// texture2d::write_bmp(filename) (texture.cpp:178-194) with clamp / quantise / BMP layout on the device.
+inline void gpu_write_bmp(shared_ptr<texture2d> rt, const std::string& filename) {
+	plu_gpu_ctx* ctx = gpu::shared_ctx();
+	int64_t n = plu_bmp_size((int32_t)rt->size.x, (int32_t)rt->size.y);
+	std::vector<unsigned char> bytes((size_t)n);
+	if (plu_gpu_encode_bmp(ctx, (int32_t)rt->size.x, (int32_t)rt->size.y, &rt->pixel(uvec2(0, 0)).x, 0, bytes.data(), n) != PLU_OK)
+		throw std::runtime_error(plu_gpu_last_error(ctx));
+	gpu_write_file(filename, bytes);
+}
+
+// main.cpp:177-209 without the watermark, with the pixels crossing PCIe once: r.render(tx) leaves the image resident on
+// the device; the tone map (main.cpp:183) and the .bmp bytes (main.cpp:209) are produced from that resident copy.  On
+// return `tx` holds the tone-mapped image exactly as after plu::postprocesser, and `filename` the reference's .bmp.
+inline void gpu_render_post_write(const gpu_renderer& r, shared_ptr<texture2d> tx, const std::string& filename) {
+	r.render(tx);
+	plu_gpu_ctx* ctx = gpu::shared_ctx();
+	if (plu_gpu_postprocess_resident(ctx, &tx->pixel(uvec2(0, 0)).x) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
+	int64_t n = plu_bmp_size((int32_t)tx->size.x, (int32_t)tx->size.y);
+	std::vector<unsigned char> bytes((size_t)n);
+	if (plu_gpu_encode_bmp_resident(ctx, 0, bytes.data(), n) != PLU_OK) throw std::runtime_error(plu_gpu_last_error(ctx));
+	gpu_write_file(filename, bytes);
 }
 }  // namespace plu

@@ -83,6 +83,7 @@ struct flat_loaded {
 	std::vector<std::shared_ptr<plu::surface>> surfs;
 	std::vector<std::shared_ptr<plu::light>> lights;
 	int samples = 0; int W = 0, H = 0;
+	std::vector<glm::vec3> tri_v, tri_n; std::vector<glm::vec2> tri_t;   // storage the triangles point into (scene.h:145-148 keeps it per mesh)
 	std::unique_ptr<plu::surfaces::bvh_tree> tree;
 };
 
@@ -117,6 +118,7 @@ void load_flat(flat_loaded& L, const std::string& path, int W, int H, int smp) {
 			default: emis[i] = std::make_shared<plu::materials::emission_material>(nullptr); mats[i] = emis[i]; break;
 		}
 	}
+	L.tri_v.resize((size_t)d->n_prims * 3); L.tri_n.resize((size_t)d->n_prims * 3); L.tri_t.resize((size_t)d->n_prims * 3);
 	for (int32_t s = 0; s < d->n_prims; ++s) {
 		const float* f = d->prim_data + (size_t)s * 12;
 		std::shared_ptr<plu::surface> surf;
@@ -125,7 +127,15 @@ void load_flat(flat_loaded& L, const std::string& path, int W, int H, int smp) {
 			auto b = std::make_shared<plu::surfaces::box>(glm::vec3(0.f), glm::vec3(0.f), nullptr);
 			b->box_bounds._min = v3of(f); b->box_bounds._max = v3of(f + 4);   // exact bits, not c -+ e again
 			surf = b;
-		} else throw std::runtime_error("render-flat: triangle meshes are not rebuilt");
+		} else {
+			glm::vec3* v = &L.tri_v[(size_t)s * 3]; glm::vec3* nn = &L.tri_n[(size_t)s * 3]; glm::vec2* tt = &L.tri_t[(size_t)s * 3];
+			for (int k = 0; k < 3; ++k) {
+				v[k] = v3of(f + 4 * k);
+				nn[k] = v3of(d->prim_tri_normal + (size_t)s * 9 + 3 * k);
+				tt[k] = glm::vec2(d->prim_tri_uv[(size_t)s * 6 + 2 * k], d->prim_tri_uv[(size_t)s * 6 + 2 * k + 1]);
+			}
+			surf = std::make_shared<plu::surfaces::triangle>(v, v + 1, v + 2, nn, nn + 1, nn + 2, tt, tt + 1, tt + 2, nullptr);
+		}
 		surf->mat = mats[(size_t)d->prim_material[s]];
 		L.surfs.push_back(surf);
 	}
@@ -244,13 +254,25 @@ int main(int argc, char** argv) {
 			plu::samplers::stratified_sampler sampler(tx->size, glm::uvec2((unsigned)n), true);
 			plu::gpu_renderer r(flat ? (plu::surface*)F.tree.get() : (plu::surface*)L.tree.get(), flat ? F.cam : L.sc->cam, glm::uvec2(32), &sampler,
 			                    flat ? F.lights : L.sc->lights);
-			auto t0 = std::chrono::high_resolution_clock::now();
-			r.render(tx);
-			auto t1 = std::chrono::high_resolution_clock::now();
+			// PLU_REF_REPEAT=k: render k times into fresh targets (the context, wave buffers and NCCL communicators of
+			// the drop-in live across calls), report the LAST call's time; PLU_REF_FUSED=1 (with a .bmp argument): the
+			// resident-framebuffer flow gpu_render_post_write, <out.bin> then holds the tone-mapped image
+			const int repeat = std::getenv("PLU_REF_REPEAT") ? std::max(1, atoi(std::getenv("PLU_REF_REPEAT"))) : 1;
+			const bool fused = argc == 8 && std::getenv("PLU_REF_FUSED") != nullptr;
+			double ms = 0.0, ms_first = 0.0;
+			for (int it = 0; it < repeat; ++it) {
+				if (it > 0) tx = std::make_shared<plu::texture2d>(glm::uvec2(w, h));
+				auto t0 = std::chrono::high_resolution_clock::now();
+				if (fused) plu::gpu_render_post_write(r, tx, argv[7]); else r.render(tx);
+				auto t1 = std::chrono::high_resolution_clock::now();
+				ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+				if (it == 0) ms_first = ms;
+			}
 			write_all(argv[6], &tx->pixel(glm::uvec2(0, 0)), (size_t)w * h * 12);
-			if (argc == 8) { plu::gpu_postprocesser pp; pp.postprocess(tx); plu::gpu_write_bmp(tx, argv[7]); }
-			printf("{\"mode\": \"%s\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f}\n", mode.c_str(),
-			       w, h, n, (unsigned long long)w * h * n * n, std::chrono::duration<double, std::milli>(t1 - t0).count());
+			if (argc == 8 && !fused) { plu::gpu_postprocesser pp; pp.postprocess(tx); plu::gpu_write_bmp(tx, argv[7]); }
+			printf("{\"mode\": \"%s\", \"width\": %d, \"height\": %d, \"smp\": %d, \"samples\": %llu, \"ms\": %.3f, \"ms_first_call\": %.3f, "
+			       "\"devices\": %d, \"ms_device\": %.3f, \"ms_reduce\": %.3f}\n", mode.c_str(),
+			       w, h, n, (unsigned long long)w * h * n * n, ms, ms_first, r.last_stats.n_devices, r.last_stats.ms_device, r.last_stats.ms_reduce);
 #endif
 		} else if (mode == "render-st" && (argc == 8 || argc == 12 || argc == 13)) {
 			int W = atoi(argv[3]), H = atoi(argv[4]), smp = atoi(argv[5]);

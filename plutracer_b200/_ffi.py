@@ -19,6 +19,7 @@ RENDER_BVH_FAST = 8
 RENDER_PROFILE = 16
 RENDER_NO_LANE_REFILL = 32
 POST_TONEMAP = 1
+ABI_VERSION = 2
 
 
 class CameraDesc(C.Structure):
@@ -63,7 +64,8 @@ class RenderStats(C.Structure):
                 ("bvh_nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64), ("ms_device", C.c_double),
                 ("ms_extend", C.c_double), ("ms_shade", C.c_double), ("ms_connect", C.c_double),
                 ("kernel_launches", C.c_uint64), ("ms_generate", C.c_double), ("ms_accumulate", C.c_double),
-                ("shade_vertices", C.c_uint64), ("shadow_entries", C.c_uint64), ("waves", C.c_uint64)]
+                ("shade_vertices", C.c_uint64), ("shadow_entries", C.c_uint64), ("waves", C.c_uint64),
+                ("ms_reduce", C.c_double), ("n_devices", C.c_int32), ("reserved", C.c_int32)]
 
 
 class BuildStats(C.Structure):
@@ -80,6 +82,8 @@ TABLE_REF_NODES, TABLE_PRIM_META, TABLE_FAST_NODES, TABLE_FAST_INDEX, TABLE_FAST
 _P = C.c_void_p
 SYMBOLS = {
     "plu_gpu_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
+    "plu_gpu_create_multi": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_P)]),
+    "plu_gpu_device_count": (C.c_int, [_P]),
     "plu_gpu_destroy": (None, [_P]),
     "plu_gpu_last_error": (C.c_char_p, [_P]),
     "plu_gpu_upload_scene": (C.c_int, [_P, C.POINTER(SceneDesc)]),
@@ -94,6 +98,8 @@ SYMBOLS = {
     "plu_bmp_size": (C.c_int64, [C.c_int32, C.c_int32]),
     "plu_gpu_encode_bmp": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, C.c_int64]),
     "plu_gpu_encode_bmp_device": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, _P, C.c_int64]),
+    "plu_gpu_postprocess_resident": (C.c_int, [_P, _P]),
+    "plu_gpu_encode_bmp_resident": (C.c_int, [_P, C.c_uint32, _P, C.c_int64]),
     "plu_scene_load_urn": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_load_flat": (C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_save_flat": (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, C.c_int32, C.c_char_p]),

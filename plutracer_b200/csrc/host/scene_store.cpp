@@ -4,6 +4,9 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <new>
+#include <stdexcept>
+#include <sys/stat.h>
 
 void plu_scene::seal() {
 	desc = plu_scene_desc{};
@@ -133,16 +136,28 @@ extern "C" int plu_scene_save_flat(const plu_scene_desc* d, int32_t width, int32
 	return ok ? PLU_OK : PLU_E_IO;
 }
 
-extern "C" int plu_scene_load_flat(const char* path, plu_scene** out, char* err, int err_len) {
-	if (!path || !out) return PLU_E_ARG;
-	*out = nullptr;
+// No exception crosses the C ABI: allocation failures and length errors of the host plumbing become error codes.
+#define PLU_GUARD_BEGIN try {
+#define PLU_GUARD_END(err, err_len)                                                                         \
+	} catch (const std::bad_alloc&) { pluhost::set_err(err, err_len, "out of host memory"); return PLU_E_NOMEM; } \
+	catch (const std::exception& e) { pluhost::set_err(err, err_len, e.what()); return PLU_E_PARSE; }
+
+static int load_flat_impl(const char* path, plu_scene** out, char* err, int err_len) {
 	FILE* f = std::fopen(path, "rb");
 	if (!f) { pluhost::set_err(err, err_len, std::string("cannot open ") + path); return PLU_E_IO; }
+	struct stat sb; int64_t file_bytes = (fstat(fileno(f), &sb) == 0) ? (int64_t)sb.st_size : -1;
 	std::unique_ptr<plu_scene> s(new plu_scene);
 	char magic[8]; int32_t head[4], counts[4]; int64_t ntex = 0;
 	bool ok = rd(f, magic, 8) && std::memcmp(magic, kMagic, 8) == 0 && rd(f, head, 4) && rd(f, &s->cam, 1) &&
 	          rd(f, counts, 4) && rd(f, &ntex, 1) && counts[0] >= 0 && counts[1] >= 0 && counts[2] >= 0 &&
 	          counts[3] >= 0 && ntex >= 0;
+	if (ok && file_bytes >= 0) {   // the counts of a truncated or corrupt header must not size the vectors
+		const int64_t n = counts[0];
+		__int128 need = (__int128)n * (4 + 4 + 48) + ((head[3] & 1) ? (__int128)n * 60 : 0) + ((head[3] & 2) ? (__int128)n * 4 : 0) +
+		                (__int128)counts[1] * (int64_t)sizeof(plu_material_desc) + (__int128)counts[2] * (int64_t)sizeof(plu_texture_desc) +
+		                (__int128)counts[3] * (int64_t)sizeof(plu_light_desc) + (__int128)ntex * 12;
+		ok = need <= (__int128)file_bytes;
+	}
 	if (ok) {
 		size_t n = (size_t)counts[0];
 		s->width = head[0]; s->height = head[1]; s->n_strata = head[2];
@@ -167,14 +182,25 @@ extern "C" int plu_scene_load_flat(const char* path, plu_scene** out, char* err,
 	return PLU_OK;
 }
 
+extern "C" int plu_scene_load_flat(const char* path, plu_scene** out, char* err, int err_len) {
+	if (!path || !out) return PLU_E_ARG;
+	*out = nullptr;
+	PLU_GUARD_BEGIN
+	return load_flat_impl(path, out, err, err_len);
+	PLU_GUARD_END(err, err_len)
+}
+
 extern "C" int plu_scene_from_desc(const plu_scene_desc* desc, int32_t width, int32_t height,
                                    int32_t n_strata, plu_scene** out) {
 	if (!out || !pluhost::validate_desc(desc).empty()) return PLU_E_ARG;
-	plu_scene* s = new plu_scene;
+	*out = nullptr;
+	PLU_GUARD_BEGIN
+	std::unique_ptr<plu_scene> s(new plu_scene);
 	pluhost::copy_desc(desc, *s);
 	s->width = width; s->height = height; s->n_strata = n_strata;
-	*out = s;
+	*out = s.release();
 	return PLU_OK;
+	PLU_GUARD_END(nullptr, 0)
 }
 
 extern "C" const plu_scene_desc* plu_scene_get_desc(const plu_scene* s) { return s ? &s->desc : nullptr; }

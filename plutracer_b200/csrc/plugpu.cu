@@ -7,12 +7,16 @@
 #include "host/bvh_build.h"
 #include "host/bvh_gpu.h"
 #include "host/scene_store.h"
+#include <nccl.h>    // types only: libnccl.so.2 is loaded at run time by plu_gpu_create_multi (no link-time dependency)
+#include <dlfcn.h>
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace plud;
@@ -49,6 +53,12 @@ struct plu_gpu_ctx {
 	uint32_t wave_hint = 0;            // paths per wave learnt from the scene's rays per path (0: not yet), see render_device
 	int n_pipes = 4;                   // waves in flight (PLU_PIPES=1..4 overrides); 2 suffice for cornell-box, launch-bound scenes gain up to 4
 	float* d_fb = nullptr; size_t fb_floats = 0;
+	int32_t res_w = 0, res_h = 0;      // size of the image plu_gpu_render left in d_fb (0: none) — plu_gpu_*_resident
+	// multi-device group (plu_gpu_create_multi): this context is devices[0]; it owns one context per further device
+	// and the NCCL communicators of the group (comms[0] is its own)
+	std::vector<plu_gpu_ctx*> peers;
+	std::vector<ncclComm_t> comms;
+	cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;   // around the framebuffer reduce
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	cudaStream_t pipe[PLU_PIPES] = {};             // wave i of a render runs on pipe[i % n_pipes]; pipe[0] is unused (= the caller's stream)
 	cudaStream_t aux[PLU_PIPES] = {};              // per pipe: the specular shade kernel of a bounce runs beside the diffuse one
@@ -107,6 +117,76 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 	return PLU_OK;
 }
 
+// ---- NCCL, loaded at run time (only multi-device contexts need it) ---------------------------------------------
+struct nccl_api {
+	void* lib = nullptr;
+	ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+	ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*GroupStart)() = nullptr;
+	ncclResult_t (*GroupEnd)() = nullptr;
+	const char* (*GetErrorString)(ncclResult_t) = nullptr;
+	std::string err;
+};
+static nccl_api* load_nccl() {
+	static nccl_api api; static std::once_flag once;
+	std::call_once(once, [] {
+		const char* names[] = {std::getenv("PLU_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+		for (const char* n : names) { if (n && *n && (api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break; }
+		if (!api.lib) { api.err = std::string("cannot load libnccl.so.2: ") + dlerror(); return; }
+#define PLU_SYM(field, name) api.field = (decltype(api.field))dlsym(api.lib, name); if (!api.field) api.err = std::string("libnccl lacks ") + name;
+		PLU_SYM(CommInitAll, "ncclCommInitAll") PLU_SYM(CommDestroy, "ncclCommDestroy") PLU_SYM(Reduce, "ncclReduce")
+		PLU_SYM(GroupStart, "ncclGroupStart") PLU_SYM(GroupEnd, "ncclGroupEnd") PLU_SYM(GetErrorString, "ncclGetErrorString")
+#undef PLU_SYM
+	});
+	return &api;
+}
+
+extern "C" int plu_gpu_create_multi(const int* devices, int n_devices, plu_gpu_ctx** out) {
+	if (!out) return PLU_E_ARG;
+	*out = nullptr;
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count <= 0) {
+		g_create_error = std::string("no usable CUDA device (libplugpu has no CPU fallback): ") + cudaGetErrorString(e);
+		return PLU_E_CUDA;
+	}
+	if (n_devices < 0 || (n_devices == 0 && devices)) { g_create_error = "n_devices must be positive"; return PLU_E_ARG; }
+	std::vector<int> devs;
+	if (!devices) { if (n_devices == 0) n_devices = count; for (int i = 0; i < n_devices; ++i) devs.push_back(i); }
+	else devs.assign(devices, devices + n_devices);
+	for (size_t i = 0; i < devs.size(); ++i) {
+		if (devs[i] < 0 || devs[i] >= count) { g_create_error = "device index out of range"; return PLU_E_ARG; }
+		for (size_t j = 0; j < i; ++j) if (devs[j] == devs[i]) { g_create_error = "device listed twice"; return PLU_E_ARG; }
+	}
+	plu_gpu_ctx* ctx = nullptr;
+	int rc = plu_gpu_create(devs[0], &ctx);
+	if (rc != PLU_OK || devs.size() == 1) { *out = ctx; return rc; }
+	for (size_t i = 1; i < devs.size(); ++i) {
+		plu_gpu_ctx* peer = nullptr;
+		rc = plu_gpu_create(devs[i], &peer);
+		if (rc != PLU_OK) { plu_gpu_destroy(ctx); return rc; }
+		ctx->peers.push_back(peer);
+	}
+	nccl_api* nc = load_nccl();
+	if (!nc->err.empty()) { g_create_error = nc->err; plu_gpu_destroy(ctx); return PLU_E_CUDA; }
+	ctx->comms.assign(devs.size(), nullptr);
+	ncclResult_t nr = nc->CommInitAll(ctx->comms.data(), (int)devs.size(), devs.data());
+	if (nr != ncclSuccess) {
+		g_create_error = std::string("ncclCommInitAll: ") + nc->GetErrorString(nr);
+		ctx->comms.clear(); plu_gpu_destroy(ctx); return PLU_E_CUDA;
+	}
+	cudaSetDevice(devs[0]);
+	if ((e = cudaEventCreate(&ctx->ev_r0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev_r1)) != cudaSuccess) {
+		g_create_error = std::string("CUDA context set-up failed: ") + cudaGetErrorString(e);
+		plu_gpu_destroy(ctx); return PLU_E_CUDA;
+	}
+	*out = ctx;
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_device_count(const plu_gpu_ctx* ctx) { return ctx ? 1 + (int)ctx->peers.size() : 0; }
+
 static void free_scene(plu_gpu_ctx* ctx) {
 	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
 	cudaFree(ctx->d_wide); ctx->d_wide = nullptr;
@@ -117,8 +197,13 @@ static void free_scene(plu_gpu_ctx* ctx) {
 
 extern "C" void plu_gpu_destroy(plu_gpu_ctx* ctx) {
 	if (!ctx) return;
+	if (!ctx->comms.empty()) { nccl_api* nc = load_nccl(); for (ncclComm_t c : ctx->comms) if (c) nc->CommDestroy(c); ctx->comms.clear(); }
+	for (plu_gpu_ctx* peer : ctx->peers) plu_gpu_destroy(peer);
+	ctx->peers.clear();
 	cudaSetDevice(ctx->device);
 	free_scene(ctx);
+	if (ctx->ev_r0) cudaEventDestroy(ctx->ev_r0);
+	if (ctx->ev_r1) cudaEventDestroy(ctx->ev_r1);
 	for (int k = 0; k < PLU_PIPES; ++k) cudaFree(ctx->d_wave[k]);
 	cudaFree(ctx->d_fb);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -183,8 +268,32 @@ __global__ void k_collapse_wide(int32_t n, const fast_node* in, wide_node* out) 
 	out[i] = W;
 }
 
+static int upload_single(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats);
+
+// A multi-device context deep-copies the scene to every device and builds the traversal structures on each (one host
+// thread per device; the builds are deterministic, so all devices hold byte-identical tables).
 extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
+	if (ctx->peers.empty()) return upload_single(ctx, d, build, stats);
+	const size_t n = ctx->peers.size();
+	std::vector<int> rc(n, PLU_OK);
+	std::vector<std::thread> th;
+	for (size_t g = 0; g < n; ++g) th.emplace_back([&, g] { rc[g] = upload_single(ctx->peers[g], d, build, nullptr); });
+	int rc0 = upload_single(ctx, d, build, stats);
+	for (auto& t : th) t.join();
+	if (rc0 != PLU_OK) return rc0;
+	for (size_t g = 0; g < n; ++g) if (rc[g] != PLU_OK) return fail(ctx, rc[g], "device " + std::to_string(ctx->peers[g]->device) + ": " + ctx->peers[g]->err);
+	return PLU_OK;
+}
+
+static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats);
+static int upload_single(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
+	try { return upload_single_impl(ctx, d, build, stats); }   // no exception crosses the C ABI (or leaves a worker thread)
+	catch (const std::bad_alloc&) { free_scene(ctx); return fail(ctx, PLU_E_NOMEM, "out of host memory while packing the scene"); }
+	catch (const std::exception& e) { free_scene(ctx); return fail(ctx, PLU_E_ARG, std::string("scene upload: ") + e.what()); }
+}
+
+static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (build != PLU_BUILD_DEVICE && build != PLU_BUILD_HOST) return fail(ctx, PLU_E_ARG, "build must be PLU_BUILD_DEVICE or PLU_BUILD_HOST");
 	std::string v = pluhost::validate_desc(d);
 	if (!v.empty()) return fail(ctx, PLU_E_ARG, v);
@@ -482,6 +591,8 @@ static int check_params(plu_gpu_ctx* ctx, const plu_render_params* p) {
 	if (p->n_strata > 32768) return fail(ctx, PLU_E_ARG, "n_strata too large");
 	if (p->max_vertices < 0 || p->max_vertices > PLU_MAX_VERTICES_CAP) return fail(ctx, PLU_E_ARG, "max_vertices out of range");
 	if (p->sample_count < 0 || (p->sample_count > 0 && (p->sample_stride <= 0 || p->sample_begin < 0))) return fail(ctx, PLU_E_ARG, "bad sample range");
+	if (p->sample_count > 0 && (int64_t)p->sample_begin + (int64_t)(p->sample_count - 1) * p->sample_stride >= (int64_t)p->n_strata * p->n_strata)
+		return fail(ctx, PLU_E_ARG, "sample range exceeds n_strata^2 (a sample index beyond the strata grid would land in the next pixel row)");
 	if (!ctx->have_scene) return fail(ctx, PLU_E_NOSCENE, "no scene uploaded");
 	return PLU_OK;
 }
@@ -497,13 +608,12 @@ static wave_desc base_desc(const plu_scene_desc*, const plu_render_params* p, co
 	return w;
 }
 
-extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb, void* stream, plu_render_stats* stats) {
-	if (!ctx) return PLU_E_ARG;
+// One device: the waves of the call's sample set on `st` (and the context's pipes), synchronised before returning.
+static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb, cudaStream_t st, plu_render_stats* stats) {
 	int rc = check_params(ctx, p);
 	if (rc != PLU_OK) return rc;
 	if (!d_rgb) return fail(ctx, PLU_E_ARG, "framebuffer pointer is NULL");
 	CU(cudaSetDevice(ctx->device));
-	cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
 	scene_ref sc = ctx->sc;
 	select_bvh(ctx, sc, p->flags);
 	wave_desc w = base_desc(nullptr, p, sc);
@@ -584,6 +694,97 @@ extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* 
 	return PLU_OK;
 }
 
+static int ensure_fb(plu_gpu_ctx* ctx, size_t floats) {
+	if (ctx->fb_floats >= floats) return PLU_OK;
+	CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0; ctx->res_w = ctx->res_h = 0;
+	CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
+	return PLU_OK;
+}
+
+// All devices of a multi-device context: device g renders the samples k = g (mod n) of the call's sample set into its
+// own framebuffer (device 0: the caller's, which already holds the pixels to add to; the others: zeroed), one host
+// thread per device enqueues that device's waves, then ONE ncclReduce(sum) to device 0 on the caller's stream.
+static int render_device_multi(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb, cudaStream_t st, plu_render_stats* stats) {
+	int rc = check_params(ctx, p);
+	if (rc != PLU_OK) return rc;
+	if (!d_rgb) return fail(ctx, PLU_E_ARG, "framebuffer pointer is NULL");
+	const int n = 1 + (int)ctx->peers.size();
+	const size_t floats = (size_t)p->width * p->height * 3;
+	const int32_t spp = p->n_strata * p->n_strata;
+	const int32_t begin = p->sample_count > 0 ? p->sample_begin : 0, stride = p->sample_count > 0 ? p->sample_stride : 1;
+	const int32_t count = p->sample_count > 0 ? p->sample_count : spp;
+	std::vector<plu_render_params> pg((size_t)n, *p);
+	std::vector<plu_render_stats> sg((size_t)n);
+	std::vector<int> rcs((size_t)n, PLU_OK);
+	for (int g = 0; g < n; ++g) {
+		pg[g].sample_begin = begin + g * stride; pg[g].sample_stride = stride * n;
+		pg[g].sample_count = g < count ? (count - g + n - 1) / n : 0;
+		std::memset(&sg[g], 0, sizeof(plu_render_stats));
+	}
+	auto run_peer = [&](int g) {
+		plu_gpu_ctx* pc = ctx->peers[(size_t)g - 1];
+		cudaError_t e = cudaSetDevice(pc->device);
+		if (e == cudaSuccess && ensure_fb(pc, floats) != PLU_OK) { rcs[g] = PLU_E_CUDA; return; }
+		if (e == cudaSuccess) e = cudaMemsetAsync(pc->d_fb, 0, floats * sizeof(float), pc->stream);
+		if (e != cudaSuccess) { pc->err = std::string("framebuffer set-up: ") + cudaGetErrorString(e); rcs[g] = PLU_E_CUDA; return; }
+		if (pg[g].sample_count > 0) rcs[g] = render_device_single(pc, &pg[g], pc->d_fb, pc->stream, &sg[g]);
+		else if (cudaStreamSynchronize(pc->stream) != cudaSuccess) rcs[g] = PLU_E_CUDA;
+	};
+	std::vector<std::thread> th;
+	for (int g = 1; g < n; ++g) th.emplace_back(run_peer, g);
+	rcs[0] = render_device_single(ctx, &pg[0], d_rgb, st, &sg[0]);   // count >= 1, so device 0 always has samples
+	for (auto& t : th) t.join();
+	for (int g = 0; g < n; ++g)
+		if (rcs[g] != PLU_OK) return g == 0 ? rcs[0] : fail(ctx, rcs[g], "device " + std::to_string(ctx->peers[(size_t)g - 1]->device) + ": " + ctx->peers[(size_t)g - 1]->err);
+	// the single collective of the path: per-device framebuffers -> device 0
+	nccl_api* nc = load_nccl();
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaEventRecord(ctx->ev_r0, st));
+	ncclResult_t nr = nc->GroupStart();
+	for (int g = 0; g < n && nr == ncclSuccess; ++g) {
+		plu_gpu_ctx* c = g == 0 ? ctx : ctx->peers[(size_t)g - 1];
+		float* buf = g == 0 ? d_rgb : c->d_fb;
+		nr = nc->Reduce(buf, buf, floats, ncclFloat32, ncclSum, 0, ctx->comms[(size_t)g], g == 0 ? st : c->stream);
+	}
+	ncclResult_t ne = nc->GroupEnd();
+	if (nr == ncclSuccess) nr = ne;
+	if (nr != ncclSuccess) return fail(ctx, PLU_E_CUDA, std::string("ncclReduce: ") + nc->GetErrorString(nr));
+	CU(cudaSetDevice(ctx->device));
+	CU(cudaEventRecord(ctx->ev_r1, st));
+	CU(cudaStreamSynchronize(st));
+	for (plu_gpu_ctx* pc : ctx->peers) { CU(cudaSetDevice(pc->device)); CU(cudaStreamSynchronize(pc->stream)); }
+	CU(cudaSetDevice(ctx->device));
+	float ms_r = 0.f; CU(cudaEventElapsedTime(&ms_r, ctx->ev_r0, ctx->ev_r1));
+	if (stats) {
+		plu_render_stats t = sg[0];
+		for (int g = 1; g < n; ++g) {
+			const plu_render_stats& a = sg[g];
+			t.samples += a.samples; t.rays_extend += a.rays_extend; t.rays_shadow += a.rays_shadow;
+			t.bvh_nodes_visited += a.bvh_nodes_visited; t.prims_tested += a.prims_tested;
+			t.kernel_launches += a.kernel_launches; t.shade_vertices += a.shade_vertices; t.shadow_entries += a.shadow_entries;
+			t.waves += a.waves;
+			t.ms_device = std::max(t.ms_device, a.ms_device);
+			t.ms_generate = std::max(t.ms_generate, a.ms_generate); t.ms_extend = std::max(t.ms_extend, a.ms_extend);
+			t.ms_shade = std::max(t.ms_shade, a.ms_shade); t.ms_connect = std::max(t.ms_connect, a.ms_connect);
+			t.ms_accumulate = std::max(t.ms_accumulate, a.ms_accumulate);
+		}
+		t.ms_reduce = ms_r; t.n_devices = n;
+		*stats = t;
+	}
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d_rgb, void* stream, plu_render_stats* stats) {
+	if (!ctx) return PLU_E_ARG;
+	// NULL is stream 0, the legacy default stream (not the context's own non-blocking stream): whatever the caller
+	// enqueued on stream 0 before this call — typically the framebuffer initialisation — is ordered before the render
+	cudaStream_t st = stream ? (cudaStream_t)stream : cudaStreamLegacy;
+	if (!ctx->peers.empty()) return render_device_multi(ctx, p, d_rgb, st, stats);
+	int rc = render_device_single(ctx, p, d_rgb, st, stats);
+	if (rc == PLU_OK && stats) { stats->ms_reduce = 0.0; stats->n_devices = 1; }
+	return rc;
+}
+
 extern "C" int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, float* out_rgb, plu_render_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
 	int rc = check_params(ctx, p);
@@ -591,16 +792,16 @@ extern "C" int plu_gpu_render(plu_gpu_ctx* ctx, const plu_render_params* p, floa
 	if (!out_rgb) return fail(ctx, PLU_E_ARG, "out_rgb is NULL");
 	CU(cudaSetDevice(ctx->device));
 	size_t floats = (size_t)p->width * p->height * 3;
-	if (ctx->fb_floats < floats) {
-		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
-		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
-	}
+	rc = ensure_fb(ctx, floats);
+	if (rc != PLU_OK) return rc;
+	ctx->res_w = ctx->res_h = 0;
 	// `+=` semantics (renderer.cpp:132): the device buffer starts from the caller's pixels
 	CU(cudaMemcpyAsync(ctx->d_fb, out_rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	rc = plu_gpu_render_device(ctx, p, ctx->d_fb, ctx->stream, stats);
 	if (rc != PLU_OK) return rc;
 	CU(cudaMemcpyAsync(out_rgb, ctx->d_fb, floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	CU(cudaStreamSynchronize(ctx->stream));
+	ctx->res_w = p->width; ctx->res_h = p->height;   // the image stays resident for plu_gpu_*_resident
 	return PLU_OK;
 }
 
@@ -705,18 +906,31 @@ extern "C" int plu_gpu_postprocess(plu_gpu_ctx* ctx, int32_t w, int32_t h, float
 	if (w <= 0 || h <= 0 || !rgb) return fail(ctx, PLU_E_ARG, "bad image arguments");
 	CU(cudaSetDevice(ctx->device));
 	size_t floats = (size_t)w * h * 3;
-	if (ctx->fb_floats < floats) {
-		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
-		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
-	}
+	int rc = ensure_fb(ctx, floats);
+	if (rc != PLU_OK) return rc;
+	ctx->res_w = ctx->res_h = 0;
 	CU(cudaMemcpyAsync(ctx->d_fb, rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	int64_t n = (int64_t)w * h;
+	ctx->res_w = w; ctx->res_h = h;
+	return plu_gpu_postprocess_resident(ctx, rgb);
+}
+
+extern "C" int plu_gpu_postprocess_resident(plu_gpu_ctx* ctx, float* rgb_out) {
+	if (!ctx) return PLU_E_ARG;
+	if (ctx->res_w <= 0 || ctx->res_h <= 0 || !ctx->d_fb) return fail(ctx, PLU_E_NOSCENE, "no resident image: plu_gpu_render has not run on this context");
+	CU(cudaSetDevice(ctx->device));
+	const int64_t n = (int64_t)ctx->res_w * ctx->res_h;
 	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
 	k_tonemap<<<grid, 256, 0, ctx->stream>>>(n, ctx->d_fb);
 	CU(cudaGetLastError());
-	CU(cudaMemcpyAsync(rgb, ctx->d_fb, floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (rgb_out) CU(cudaMemcpyAsync(rgb_out, ctx->d_fb, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	CU(cudaStreamSynchronize(ctx->stream));
 	return PLU_OK;
+}
+
+extern "C" int plu_gpu_encode_bmp_resident(plu_gpu_ctx* ctx, uint32_t flags, unsigned char* out, int64_t cap) {
+	if (!ctx) return PLU_E_ARG;
+	if (ctx->res_w <= 0 || ctx->res_h <= 0 || !ctx->d_fb) return fail(ctx, PLU_E_NOSCENE, "no resident image: plu_gpu_render has not run on this context");
+	return plu_gpu_encode_bmp_device(ctx, ctx->res_w, ctx->res_h, ctx->d_fb, flags, ctx->stream, out, cap);
 }
 
 extern "C" int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t w, int32_t h, const float* d_rgb, uint32_t flags, void* stream,
@@ -726,7 +940,7 @@ extern "C" int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t w, int32_t h,
 	const int64_t total = plu_bmp_size(w, h);
 	if (cap < total) return fail(ctx, PLU_E_ARG, "output buffer smaller than plu_bmp_size");
 	CU(cudaSetDevice(ctx->device));
-	cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+	cudaStream_t st = stream ? (cudaStream_t)stream : cudaStreamLegacy;
 	unsigned char* d_body = nullptr;
 	CU(cudaMalloc(&d_body, (size_t)(total - 54)));
 	int64_t n = (int64_t)w * h;
@@ -746,11 +960,11 @@ extern "C" int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t w, int32_t h, const 
 	if (w <= 0 || h <= 0 || !rgb || !out) return fail(ctx, PLU_E_ARG, "bad image arguments");
 	CU(cudaSetDevice(ctx->device));
 	size_t floats = (size_t)w * h * 3;
-	if (ctx->fb_floats < floats) {
-		CU(cudaFree(ctx->d_fb)); ctx->d_fb = nullptr; ctx->fb_floats = 0;
-		CU(cudaMalloc(&ctx->d_fb, floats * sizeof(float))); ctx->fb_floats = floats;
-	}
+	int rc = ensure_fb(ctx, floats);
+	if (rc != PLU_OK) return rc;
+	ctx->res_w = ctx->res_h = 0;
 	CU(cudaMemcpyAsync(ctx->d_fb, rgb, floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	ctx->res_w = w; ctx->res_h = h;
 	return plu_gpu_encode_bmp_device(ctx, w, h, ctx->d_fb, flags, ctx->stream, out, cap);
 }
 

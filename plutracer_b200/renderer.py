@@ -19,16 +19,38 @@ from .scene import Scene, stratified_sampler, texture2d  # noqa: F401  (re-expor
 DEFAULT_SEED = 20261104
 
 
+def devices_from_env(default=0):
+    """PLU_DEVICES="0,1,2,3" | "all" | unset (-> `default`): the device list of the drop-in, as
+    integration/plu_gpu_renderer.h reads it."""
+    import os
+    v = os.environ.get("PLU_DEVICES", "").strip()
+    if not v:
+        return default
+    if v.lower() == "all":
+        return "all"
+    return [int(x) for x in v.split(",") if x.strip()]
+
+
 class GpuContext:
-    """One libplugpu context = one CUDA device (one process per GPU)."""
+    """One libplugpu context: one CUDA device (`device` an int: one process per GPU), or several GPUs of
+    the box driven from this process (`device` a list of ints, or "all"): plu_gpu_create_multi — the scene is
+    replicated, samples are split k = g (mod n) and the framebuffers are combined by one NCCL reduce."""
 
     def __init__(self, device=0):
         self._lib = _ffi.lib()
         self._h = C.c_void_p()
-        rc = self._lib.plu_gpu_create(int(device), C.byref(self._h))
+        if isinstance(device, (list, tuple)) or device == "all":
+            if device == "all":
+                rc = self._lib.plu_gpu_create_multi(None, 0, C.byref(self._h))
+            else:
+                arr = (C.c_int * len(device))(*[int(d) for d in device])
+                rc = self._lib.plu_gpu_create_multi(arr, len(device), C.byref(self._h))
+        else:
+            rc = self._lib.plu_gpu_create(int(device), C.byref(self._h))
         if rc != _ffi.PLU_OK:
             raise _ffi.PluError(rc, self._lib.plu_gpu_last_error(None).decode(errors="replace"))
-        self.device = int(device)
+        self.n_devices = int(self._lib.plu_gpu_device_count(self._h))
+        self.device = device if isinstance(device, int) else (0 if device == "all" else int(device[0]))
         self._scene = None
 
     def _check(self, rc):
@@ -102,6 +124,18 @@ class GpuContext:
         assert rgb.dtype == np.float32 and rgb.flags.c_contiguous and rgb.ndim == 3 and rgb.shape[2] == 3
         self._check(self._lib.plu_gpu_postprocess(self._h, rgb.shape[1], rgb.shape[0], rgb.ctypes.data))
         return rgb
+
+    def postprocess_resident(self, out=None):
+        """Tone-map the image the last render() left on the device, in place there; `out` (host float32) receives it."""
+        self._check(self._lib.plu_gpu_postprocess_resident(self._h, out.ctypes.data if out is not None else None))
+        return out
+
+    def encode_bmp_resident(self, size, tonemap=False):
+        """.bmp bytes of the resident image (size = (W, H) of the last render)."""
+        n = self._lib.plu_bmp_size(int(size[0]), int(size[1]))
+        out = np.zeros(n, np.uint8)
+        self._check(self._lib.plu_gpu_encode_bmp_resident(self._h, _ffi.POST_TONEMAP if tonemap else 0, out.ctypes.data, n))
+        return out
 
     def encode_bmp(self, rgb, tonemap=False, device_ptr=None, size=None, stream=None):
         """The bytes texture2d::write_bmp (texture.cpp:178-194) writes, from a host float32 (H, W, 3) image or,

@@ -142,7 +142,7 @@ def scene_from_tables(cam, prim_tag, prim_material, prim_data, materials, lights
     mat = np.ascontiguousarray(prim_material, np.int32)
     data = np.ascontiguousarray(prim_data, np.float32).reshape(n, 12)
     d = _ffi.SceneDesc()
-    d.abi_version = 1
+    d.abi_version = _ffi.ABI_VERSION
     d.cam = cam
     d.n_prims, d.n_materials, d.n_textures, d.n_lights = n, len(materials), len(textures), len(lights)
     fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int32)

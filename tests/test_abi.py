@@ -19,7 +19,7 @@ def test_header_symbols_all_exported(lib):
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in plugpu.h but not exported by libplugpu.so"
     assert declared == set(_ffi.SYMBOLS), declared ^ set(_ffi.SYMBOLS)
-    assert lib.plu_abi_version() == 1
+    assert lib.plu_abi_version() == _ffi.ABI_VERSION == 2
 
 
 def test_struct_sizes_match_header(lib):
@@ -29,7 +29,7 @@ def test_struct_sizes_match_header(lib):
     assert C.sizeof(_ffi.TextureDesc) == 12 * 4
     assert C.sizeof(_ffi.LightDesc) == 10 * 4
     assert C.sizeof(_ffi.RenderParams) == 48
-    assert C.sizeof(_ffi.RenderStats) == 120
+    assert C.sizeof(_ffi.RenderStats) == 136
 
 
 def test_no_cpu_fallback(lib):

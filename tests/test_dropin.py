@@ -16,6 +16,7 @@ from tests.test_oracle import same_bits
 
 pytestmark = pytest.mark.gpu
 BIN = os.path.join(ROOT, "oracle", "_ref", "plu_ref_gpu")
+ONE_GPU = dict(os.environ, PLU_DEVICES="0")   # bit-identity holds on one device; all visible devices: tests/test_multi_gpu.py
 
 
 def _need_bin():
@@ -39,7 +40,7 @@ def test_reference_object_graph_through_gpu_renderer(lib, tmp_path, name):
     _need_bin()
     w, h, n = 64, 48, 4
     out = str(tmp_path / "img.bin")
-    res = subprocess.run([BIN, "render-gpu-flat", os.path.join(GOLDEN, name + ".pluscene"), str(w), str(h), str(n), out], capture_output=True, text=True)
+    res = subprocess.run([BIN, "render-gpu-flat", os.path.join(GOLDEN, name + ".pluscene"), str(w), str(h), str(n), out], capture_output=True, text=True, env=ONE_GPU)
     assert res.returncode == 0, res.stderr
     got = np.fromfile(out, np.float32).reshape(h, w, 3)
     tx, _ = _own_render(golden_scene(name, w, h, n), w, h, n)
@@ -56,7 +57,7 @@ def test_reference_loader_through_gpu_renderer_and_bmp(lib, tmp_path, name):
     w, h, n = 64, 48, 3
     out, bmp = str(tmp_path / "img.bin"), str(tmp_path / "img.bmp")
     scenes = os.path.join(ROOT, "scenes")
-    res = subprocess.run([BIN, "render-gpu", os.path.join(scenes, name + ".urn"), str(w), str(h), str(n), out, bmp], capture_output=True, text=True, cwd=scenes)
+    res = subprocess.run([BIN, "render-gpu", os.path.join(scenes, name + ".urn"), str(w), str(h), str(n), out, bmp], capture_output=True, text=True, cwd=scenes, env=ONE_GPU)
     assert res.returncode == 0, res.stderr
     got = np.fromfile(out, np.float32).reshape(h, w, 3)
     cwd = os.getcwd()
