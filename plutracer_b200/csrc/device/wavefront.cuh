@@ -20,6 +20,18 @@
 
 namespace plud {
 
+struct wave_desc {
+	int32_t width, height;      // target->size
+	int32_t n_strata;           // sample_count.x
+	int32_t pix0, npix;         // pixel range of this wave (row-major; >= W*H: overflow-column strip, row = pix - W*H)
+	int32_t k0, kcount;         // ordinals of the samples of this wave
+	int32_t sample_begin, sample_stride;   // sample index s = begin + (k0 + k) * stride
+	int32_t max_vertices;
+	uint32_t seed_lo, seed_hi;
+	uint32_t n_slots;           // npix * kcount
+	int32_t use_lens;
+};
+
 struct wave_buffers {
 	// Path state: one 64-byte record per slot = one DRAM access atom.  Queues hold slot ids, so state is
 	// GATHERED by index; with one array per field every 16-byte gather dragged a 64-byte atom from HBM
@@ -36,6 +48,10 @@ struct wave_buffers {
 	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
 	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_SHADOW, CNT_HIT_DIFFUSE, CNT_HIT_SPECULAR}]
 	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries
+	// The wave's descriptor lives in DEVICE memory (copied there ahead of the wave), not in kernel parameters: the launch
+	// sequence of a wave is then identical for every wave of a render and is replayed as ONE CUDA graph launch per wave
+	// (plugpu.cu: wave_graph) instead of ~60 driver calls — short-path scenes were bound by the host's launch rate.
+	const wave_desc* desc;
 };
 
 // one 128-byte line per bounce, one 32-byte sector per counter a kernel adds to; the two hit counters are
@@ -62,17 +78,6 @@ struct wave_buffers {
 #define SH_NEED2 2u
 #define SH_DELTA 4u
 
-struct wave_desc {
-	int32_t width, height;      // target->size
-	int32_t n_strata;           // sample_count.x
-	int32_t pix0, npix;         // pixel range of this wave (row-major; >= W*H: overflow-column strip, row = pix - W*H)
-	int32_t k0, kcount;         // ordinals of the samples of this wave
-	int32_t sample_begin, sample_stride;   // sample index s = begin + (k0 + k) * stride
-	int32_t max_vertices;
-	uint32_t seed_lo, seed_hi;
-	uint32_t n_slots;           // npix * kcount
-	int32_t use_lens;
-};
 
 PLU_DEV void slot_to_path(const wave_desc& w, uint32_t slot, philox_key& key, int32_t& px, int32_t& py, int32_t& s) {
 	uint32_t q = slot % (uint32_t)w.npix, k = slot / (uint32_t)w.npix;
@@ -132,7 +137,8 @@ extern __shared__ uint4 plu_smem[];
 // ---- k_generate -----------------------------------------------------------------------------------------------
 // stratified_sampler::generate_samples for one sample (sampler.h:58-69): stratum (s % n, s / n),
 // px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.
-__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb) {
+__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb) {
+	const wave_desc w = *wb.desc;
 	for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < w.n_slots; slot += gridDim.x * blockDim.x) {
 		philox_key key; int32_t px_x, px_y, s;
 		slot_to_path(w, slot, key, px_x, px_y, s);
@@ -191,11 +197,11 @@ PLU_DEV int extend_finish(const scene_ref& sc, float4* recs, float4* rad, int bo
 // into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
 // the queue entry of iteration i+2; queue pushes started in iteration i are completed in iteration i+1.
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce, uint32_t n_identity) {
+__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
-	const uint32_t n = bounce == 0 ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
+	const uint32_t n = bounce == 0 ? wb.desc->n_slots : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	if (blockIdx.x * PLU_CTA >= n) return;   // a CTA without a first entry has no work: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
@@ -301,11 +307,11 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 #endif
 
 template <bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce, uint32_t n_identity, uint32_t refill) {
+__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	float4* const recs = wb.rec;
 	const bool ident = bounce == 0;
-	const uint32_t n = ident ? n_identity : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
+	const uint32_t n = ident ? wb.desc->n_slots : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	const uint32_t* q = wb.queue[bounce & 1];
 	unsigned long long* cnt_pair = (unsigned long long*)(wb.counters + bounce * CNT_STRIDE + CNT_HIT_DIFFUSE);   // (diffuse, specular)
 	uint32_t* work = wb.counters + bounce * CNT_STRIDE + CNT_WORK;
@@ -379,8 +385,9 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
 	scene_ref sc = sc_in;
+	const wave_desc w = *wb.desc;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];

@@ -50,7 +50,11 @@ struct plu_gpu_ctx {
 	uint32_t cap[PLU_PIPES] = {};      // path slots
 	wave_buffers wbs[PLU_PIPES] = {};
 	void* d_wave[PLU_PIPES] = {};
-	uint32_t wave_hint = 0;            // paths per wave learnt from the scene's rays per path (0: not yet), see render_device
+	// One CUDA graph per pipe = the whole launch sequence of a wave (generate -> [extend, shade, shade, connect] x depth);
+	// valid while its key (scene tables, kernel variants, grids, buffers) is unchanged, see wave_graph_for()
+	struct wave_graph { cudaGraphExec_t exec = nullptr; std::vector<unsigned char> key; int launches = 0; };
+	wave_graph graphs[PLU_PIPES];
+	wave_desc* h_descs = nullptr; size_t h_descs_cap = 0;   // pinned: the descriptors of a render's waves, copied to wb.desc wave by wave
 	int n_pipes = 4;                   // waves in flight (PLU_PIPES=1..4 overrides); 2 suffice for cornell-box, launch-bound scenes gain up to 4
 	float* d_fb = nullptr; size_t fb_floats = 0;
 	int32_t res_w = 0, res_h = 0;      // size of the image plu_gpu_render left in d_fb (0: none) — plu_gpu_*_resident
@@ -204,7 +208,8 @@ extern "C" void plu_gpu_destroy(plu_gpu_ctx* ctx) {
 	free_scene(ctx);
 	if (ctx->ev_r0) cudaEventDestroy(ctx->ev_r0);
 	if (ctx->ev_r1) cudaEventDestroy(ctx->ev_r1);
-	for (int k = 0; k < PLU_PIPES; ++k) cudaFree(ctx->d_wave[k]);
+	for (int k = 0; k < PLU_PIPES; ++k) { cudaFree(ctx->d_wave[k]); if (ctx->graphs[k].exec) cudaGraphExecDestroy(ctx->graphs[k].exec); }
+	if (ctx->h_descs) cudaFreeHost(ctx->h_descs);
 	cudaFree(ctx->d_fb);
 	if (ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -418,7 +423,6 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 	}
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
-	ctx->wave_hint = 0;
 	CU(cudaDeviceSynchronize());   // pageable uploads have landed before any stream renders from them
 	ctx->have_scene = true;
 	return PLU_OK;
@@ -453,13 +457,16 @@ static void select_bvh(const plu_gpu_ctx* ctx, scene_ref& sc, uint32_t flags) {
 
 // ---- wave buffers ---------------------------------------------------------------------------------------------
 #define PLU_MAX_VERTICES_CAP 64
+#ifndef PLU_WAVE_PATHS
+#define PLU_WAVE_PATHS (1u << 22)
+#endif
 
 static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	if (ctx->cap[P] >= slots && ctx->d_wave[P]) return PLU_OK;
 	CU(cudaFree(ctx->d_wave[P])); ctx->d_wave[P] = nullptr; ctx->cap[P] = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long));
+	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long)) + al(sizeof(wave_desc));
 	CU(cudaMalloc(&ctx->d_wave[P], bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave[P];
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
@@ -472,6 +479,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
+	wb.desc = (const wave_desc*)take(sizeof(wave_desc));
 	if ((size_t)(p - (unsigned char*)ctx->d_wave[P]) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
 	ctx->cap[P] = slots;
 	return PLU_OK;
@@ -529,12 +537,15 @@ struct wave_profiler {
 };
 
 // Enqueue one wave (generate -> [extend, shade, connect] x max_vertices); returns the launch count.
-static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& w, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr, int P = 0) {
+// The wave's descriptor must already be on its way to wb.desc on `st` (put_desc); nothing here depends on the wave, so the
+// same sequence serves every wave of a render (and is what wave_graph_for captures).
+static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr, int P = 0) {
 	wave_buffers& wb = ctx->wbs[P];
 	wave_profiler none; if (!pf) pf = &none;
+	struct { int max_vertices; } w{max_vertices};
 	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);
 	pf->mark(-1, st);
-	k_generate<<<c.g_gen, 256, 0, st>>>(sc, w, wb);
+	k_generate<<<c.g_gen, 256, 0, st>>>(sc, wb);
 	pf->mark(0, st);
 	int launches = 1;
 	// the two shade kernels of a bounce touch disjoint slots and push through atomics: the specular one (few vertices,
@@ -542,15 +553,15 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 	const bool fork = ctx->has_specular && !pf->on && !c.no_fork;
 	for (int b = 0; b < w.max_vertices; ++b) {
 		if (c.smem) {
-			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
-			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
+			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
 			pf->mark(1, st);
 			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
-			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
+			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
 			if (ctx->has_specular) {
 				cudaStream_t s2 = fork ? ctx->aux[P] : st;
 				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
-				k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
+				k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b); launches++;
 				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
 			}
 			pf->mark(2, st);
@@ -561,17 +572,17 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 			// fast BVH, no sphere (whose non-unit-direction rays need the reference tree): persistent warps with lane refill
 			const bool pt = sc.fast_nodes != nullptr && !sc.has_spheres && !c.no_pt;
 			if (pt) {
-				if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, w.n_slots, ctx->pt_refill);
-				else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, w.n_slots, ctx->pt_refill);
-			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
-			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b, w.n_slots);
+				if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+				else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
 			pf->mark(1, st);
 			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
-			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, w, wb, b);
+			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
 			if (ctx->has_specular) {
 				cudaStream_t s2 = fork ? ctx->aux[P] : st;
 				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
-				k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, w, wb, b); launches++;
+				k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b); launches++;
 				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
 			}
 			pf->mark(2, st);
@@ -582,6 +593,45 @@ static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, const wave_desc& 
 		launches += 3;
 	}
 	return launches;
+}
+
+// The pinned descriptor array of a render (one entry per wave; an entry is read by its async copy when the stream gets
+// there, so entries are never reused inside a render).
+static int ensure_descs(plu_gpu_ctx* ctx, size_t n) {
+	if (ctx->h_descs_cap >= n) return PLU_OK;
+	if (ctx->h_descs) { CU(cudaFreeHost(ctx->h_descs)); ctx->h_descs = nullptr; ctx->h_descs_cap = 0; }
+	size_t cap = std::max<size_t>(n, 1024);
+	CU(cudaHostAlloc(&ctx->h_descs, cap * sizeof(wave_desc), cudaHostAllocDefault));
+	ctx->h_descs_cap = cap;
+	return PLU_OK;
+}
+
+// The graph of one wave on pipe P (launch sequence of enqueue_wave, captured once and replayed for every wave).  It is
+// rebuilt when anything a kernel parameter was captured from changes: the scene tables, the kernel variants and grids,
+// the path-length limit, the pipe's buffers or streams.  Returns nullptr when the capture fails (the caller then
+// enqueues the launches directly — same kernels either way).
+static plu_gpu_ctx::wave_graph* wave_graph_for(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, int P) {
+	std::vector<unsigned char> key;
+	auto put = [&](const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; key.insert(key.end(), b, b + n); };
+	put(&sc, sizeof(sc)); put(&c, sizeof(c)); put(&max_vertices, sizeof(max_vertices)); put(&ctx->wbs[P], sizeof(wave_buffers));
+	put(&st, sizeof(st)); put(&ctx->has_specular, sizeof(bool)); put(&ctx->pt_refill, sizeof(uint32_t));
+	plu_gpu_ctx::wave_graph& g = ctx->graphs[P];
+	if (g.exec && g.key == key) return &g;
+	if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+	cudaGraph_t graph = nullptr;
+	if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+	g.launches = enqueue_wave(ctx, sc, max_vertices, c, st, nullptr, P);
+	cudaError_t e = cudaStreamEndCapture(st, &graph);
+	if (e == cudaSuccess) e = cudaGraphInstantiate(&g.exec, graph, 0);
+	if (graph) cudaGraphDestroy(graph);
+	if (e != cudaSuccess) { cudaGetLastError(); g.exec = nullptr; return nullptr; }
+	g.key.swap(key);
+	return &g;
+}
+
+static int put_desc(plu_gpu_ctx* ctx, const wave_desc* host, cudaStream_t st, int P) {
+	CU(cudaMemcpyAsync((void*)ctx->wbs[P].desc, host, sizeof(wave_desc), cudaMemcpyHostToDevice, st));
+	return PLU_OK;
 }
 
 static int check_params(plu_gpu_ctx* ctx, const plu_render_params* p) {
@@ -621,9 +671,9 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	const int32_t spp = p->n_strata * p->n_strata;
 	const int32_t count = p->sample_count > 0 ? p->sample_count : spp;
 	const float smp_wgt = 1.f / (float)(uint32_t)spp;   // renderer.cpp:100
-	// paths per wave: 2^22 unless an earlier render of this scene showed short paths (few rays per path = many nearly
-	// empty launches per wave), for which larger waves amortise the per-launch cost: glass0 15.2 -> 19.2 Gsamples/s
-	uint32_t want = p->strata_per_wave > 0 ? (uint32_t)std::min<int64_t>(wh * p->strata_per_wave, (int64_t)1 << 26) : (ctx->wave_hint ? ctx->wave_hint : (1u << 22));
+	// paths per wave: a fixed default (PLU_WAVE_PATHS) or the caller's strata_per_wave — no state learnt from earlier
+	// renders: with one graph launch per wave the host cost per wave no longer depends on the path length
+	uint32_t want = p->strata_per_wave > 0 ? (uint32_t)std::min<int64_t>(wh * p->strata_per_wave, (int64_t)1 << 26) : PLU_WAVE_PATHS;
 	want = (uint32_t)std::min<int64_t>(want, wh * (int64_t)count);
 	want = std::max<uint32_t>(want, (uint32_t)std::min<int64_t>(wh, 1 << 22));
 	rc = ensure_wave(ctx, want);
@@ -631,6 +681,7 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
 	cfg.no_pt = (p->flags & PLU_RENDER_NO_LANE_REFILL) != 0;
 	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
+	const bool use_graph = !prof.on && std::getenv("PLU_NO_GRAPH") == nullptr;
 	// Two waves in flight: even waves on the caller's stream, odd waves on ctx->pipe1 with the second buffer set.
 	// Every kernel of a wave is a full-occupancy persistent grid whose CTAs end at different times; with two
 	// independent waves the SMs one wave's kernel leaves idle at its tail (and between its launches) run the other
@@ -643,6 +694,8 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	for (int k = 1; k < NP; ++k)
 		if (ensure_wave(ctx, want, k) != PLU_OK) { cudaGetLastError(); NP = k; break; }   // no memory for another set: fewer waves in flight
 	const bool two = NP > 1;
+	rc = ensure_descs(ctx, (size_t)waves_total + (size_t)((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? (int64_t)count * ((p->height + wcap - 1) / wcap) : 0));
+	if (rc != PLU_OK) return rc;
 	for (int k = 0; k < NP; ++k) CU(cudaMemsetAsync(ctx->wbs[k].stats, 0, 8 * sizeof(unsigned long long), st));
 	CU(cudaEventRecord(ctx->ev0, st));
 	if (two) { CU(cudaEventRecord(ctx->ev_start, st)); for (int k = 1; k < NP; ++k) CU(cudaStreamWaitEvent(ctx->pipe[k], ctx->ev_start, 0)); }
@@ -658,7 +711,13 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 				w.n_slots = (uint32_t)(np * w.kcount);
 				const int P = (int)(waves % (uint64_t)NP);
 				cudaStream_t sp = P ? ctx->pipe[P] : st;
-				launches += (uint64_t)enqueue_wave(ctx, sc, w, cfg, sp, &prof, P);
+				if (waves >= ctx->h_descs_cap) return fail(ctx, PLU_E_NOMEM, "wave descriptor array too small");
+				ctx->h_descs[waves] = w;
+				rc = put_desc(ctx, ctx->h_descs + waves, sp, P);
+				if (rc != PLU_OK) return rc;
+				plu_gpu_ctx::wave_graph* wg = use_graph ? wave_graph_for(ctx, sc, w.max_vertices, cfg, sp, P) : nullptr;
+				if (wg) { CU(cudaGraphLaunch(wg->exec, sp)); launches += (uint64_t)wg->launches; }
+				else launches += (uint64_t)enqueue_wave(ctx, sc, w.max_vertices, cfg, sp, &prof, P);
 				if (two && waves > 0) CU(cudaStreamWaitEvent(sp, ctx->ev_acc[(P + NP - 1) % NP], 0));   // the previous wave's add
 				k_accumulate<<<cfg.g_acc, 256, 0, sp>>>(w, ctx->wbs[P], d_rgb, smp_wgt);
 				if (two) CU(cudaEventRecord(ctx->ev_acc[P], sp));
@@ -686,10 +745,6 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 		stats->shade_vertices = h[4]; stats->shadow_entries = h[5]; stats->waves = waves;
 		stats->ms_generate = prof.ms[0]; stats->ms_extend = prof.ms[1]; stats->ms_shade = prof.ms[2];
 		stats->ms_connect = prof.ms[3]; stats->ms_accumulate = prof.ms[4];
-		if (samples >= (1u << 20) && std::getenv("PLU_NO_WAVE_HINT") == nullptr) {   // enough paths for a stable ratio
-			double r = (double)(h[0] + h[1]) / (double)samples;
-			ctx->wave_hint = r < 2.0 ? (1u << 24) : (r < 3.5 ? (1u << 23) : (1u << 22));
-		}
 	}
 	return PLU_OK;
 }
@@ -871,7 +926,9 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 		for (int32_t k0 = 0; k0 < count; k0 += K) {
 			w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
 			w.n_slots = (uint32_t)(np * w.kcount);
-			enqueue_wave(ctx, sc, w, cfg, ctx->stream);
+			rc = put_desc(ctx, &w, ctx->stream, 0);   // pageable source: staged before the call returns
+			if (rc != PLU_OK) return rc;
+			enqueue_wave(ctx, sc, w.max_vertices, cfg, ctx->stream);
 			CU(cudaGetLastError());
 			host.resize(w.n_slots);
 			CU(cudaMemcpyAsync(host.data(), ctx->wbs[0].rad, (size_t)w.n_slots * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));

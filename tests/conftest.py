@@ -34,6 +34,33 @@ def gpu(lib):
     ctx.close()
 
 
+_PARITY = {}
+
+
+def record_parity(key, metrics):
+    """Keep the converged-image statistics of a test run: written at session end to $PLU_PARITY_OUT (default
+    gpurun_out/parity_metrics.json, the directory gpurun brings back; copied to profiles/r02_parity.json)."""
+    _PARITY[key] = metrics
+
+
+def pytest_sessionfinish(session, exitstatus):
+    if not _PARITY:
+        return
+    import json
+    path = os.environ.get("PLU_PARITY_OUT", os.path.join(ROOT, "gpurun_out", "parity_metrics.json"))
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        old = {}
+        if os.path.exists(path):
+            with open(path) as f:
+                old = json.load(f)
+        old.update(_PARITY)
+        with open(path, "w") as f:
+            json.dump(old, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
 REF_SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's scenes (BASELINE.json configs)
 OWN_SCENES = ["atrium", "colonnade", "shard", "gallery"]                         # scenes/ of this repo
 SCENES = REF_SCENES + OWN_SCENES

@@ -76,6 +76,9 @@ def main():
     ap.add_argument("--converged", action="store_true")
     ap.add_argument("--only", default="", help="regenerate one scene only (own seeded ray set)")
     ap.add_argument("--big", default="", help="path of a pre-rendered cornell 256x256 /smp 64 pair prefix (a/b .bin)")
+    ap.add_argument("--bands1024", default="", help="directory of pre-rendered cornell-box bands at the 1024x1024 camera, /smp 64 "
+                    "(plu_ref render-st <urn> 1024 1024 64 <seed> s<seed>_y<y0>.bin 0 y0 1024 y0+32, seeds 101 and 202): "
+                    "-> cornell-box.converged1024.npz")
     args = ap.parse_args()
     if not os.path.exists(REF_BIN):
         sys.exit("build oracle/_ref/plu_ref first (make -C oracle)")
@@ -131,5 +134,24 @@ def main():
         np.savez_compressed(f"{HERE}/cornell-box.converged256.npz", cfg=np.array([256, 256, 64]), a=a, b=b)
 
 
+def pack_bands1024(directory):
+    """BASELINE.json configs[1] at ITS size: the reference's own 4096-spp render of cornell-box with the 1024x1024 camera,
+    as eight 32-row bands (a quarter of the image, evenly spaced), two independent seeds.  One band is 134 M paths =
+    ~8 min of one core; `for seed in 101 202; for y0 in 96 224 352 480 608 736 864 992: plu_ref render-st
+    cornell-box.urn 1024 1024 64 $seed s${seed}_y${y0}.bin 0 $y0 1024 $((y0+32))` (8 processes at a time)."""
+    import glob
+    import re
+    y0s = sorted({int(re.search(r"_y(\d+)\.bin$", f).group(1)) for f in glob.glob(os.path.join(directory, "s101_y*.bin"))})
+    out = {}
+    for tag, seed in (("a", 101), ("b", 202)):
+        out[tag] = np.stack([np.fromfile(os.path.join(directory, f"s{seed}_y{y0}.bin"), np.float32).reshape(32, 1024, 3) for y0 in y0s])
+    np.savez_compressed(f"{HERE}/cornell-box.converged1024.npz", cfg=np.array([1024, 1024, 64]), y0=np.array(y0s), rows=np.array(32),
+                        seeds=np.array([101, 202]), **out)
+    print("bands", y0s, "mean a", float(np.nanmean(out["a"])), "mean b", float(np.nanmean(out["b"])))
+
+
 if __name__ == "__main__":
-    main()
+    if "--bands1024" in sys.argv:
+        pack_bands1024(sys.argv[sys.argv.index("--bands1024") + 1])
+    else:
+        main()

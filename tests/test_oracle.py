@@ -107,4 +107,7 @@ def test_philox_stream_converges_to_reference_renders(oracle, name):
     w, h, n = (int(v) for v in g["cfg"])
     sc = golden_scene(name, w, h, n)
     img, _ = oracle.render(sc, GpuContext.params(w, h, n, seed=424242, flags=1), trig=0)
-    check_converged(converged_metrics(img, g["a"], g["b"]), w * h)
+    m = converged_metrics(img, g["a"], g["b"])
+    from tests.conftest import record_parity
+    record_parity(f"oracle:{name}:{w}x{h}:/smp{n}", m)
+    check_converged(m, w * h, name)
