@@ -57,6 +57,14 @@ CONFIGS = {
 }
 
 
+def config_names(arg):
+    names = list(CONFIGS) if arg == "all" else [x for x in arg.split(",") if x]
+    for x in names:
+        if x not in CONFIGS:
+            raise SystemExit(f"unknown --config {x!r}: one of {', '.join(CONFIGS)}, all")
+    return names
+
+
 def env_int(name, default):
     try:
         return int(os.environ.get(name, default))
@@ -216,8 +224,7 @@ def main_reference(args):
     rank = env_int("RANK", 0)
     if rank != 0:
         return 0
-    names = list(CONFIGS) if args.config == "all" else [args.config]
-    for name in names:
+    for name in config_names(args.config):
         c = CONFIGS[name]
         # a bounded sample per step: ~4 M paths of the same workload (synthetic: 16 K primary samples, the reference's
         # tree makes every ray visit thousands of nodes)
@@ -474,7 +481,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--config", default=DEFAULT_CONFIG, choices=list(CONFIGS) + ["all"])
+    ap.add_argument("--config", default=DEFAULT_CONFIG, help="a configuration name, a comma-separated list, or 'all' (see the module docstring)")
     ap.add_argument("--spp-per-step", type=int, default=0, help="render only the first k strata per step (0: the configuration's n^2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--strata-per-wave", type=int, default=0, help="paths in flight = W*H*this (0: library default)")
@@ -495,8 +502,7 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON lines only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         host_group = dist.new_group(backend="gloo")
-    names = list(CONFIGS) if args.config == "all" else [args.config]
-    for name in names:
+    for name in config_names(args.config):
         bench_config(name, args, rank, world, local, host_group)
     if world > 1:
         dist.barrier()

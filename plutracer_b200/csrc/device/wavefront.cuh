@@ -30,6 +30,7 @@ struct wave_desc {
 	uint32_t seed_lo, seed_hi;
 	uint32_t n_slots;           // npix * kcount
 	int32_t use_lens;
+	int32_t use_dirty;          // 1: the wave started with k_primary — rad[slot] is only valid where the slot's dirty bit is set
 };
 
 struct wave_buffers {
@@ -43,11 +44,12 @@ struct wave_buffers {
 	// path_throughput ping-pongs by vertex parity: k_connect of vertex v still needs T before the vertex.
 	float4* rec;
 	float4* rad;          // L
+	uint32_t* dirty;      // one bit per slot (k_primary): 0 = the camera ray missed, L == 0 and rad[slot] was never written
 	uint32_t* queue[2];   // extend queues, ping-pong
 	uint32_t* q_hit[2];   // paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR)
 	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
 	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_SHADOW, CNT_HIT_DIFFUSE, CNT_HIT_SPECULAR}]
-	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries
+	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries, 6 graph loop rounds
 	// The wave's descriptor lives in DEVICE memory (copied there ahead of the wave), not in kernel parameters: the launch
 	// sequence of a wave is then identical for every wave of a render and is replayed as ONE CUDA graph launch per wave
 	// (plugpu.cu: wave_graph) instead of ~60 driver calls — short-path scenes were bound by the host's launch rate.
@@ -122,6 +124,15 @@ PLU_DEV void cp_async_8(void* smem_dst, const void* gsrc) {
 PLU_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> PLU_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// Path vertex of a launch: a literal index, or — inside the while loop of a wave's CUDA graph, where every iteration runs
+// the same kernel nodes — the loop counter in device memory (row max_vertices + 1 of the counters, cleared with them).
+#define PLU_B_LOOP (-1)        // the vertex the loop is at
+#define PLU_B_LOOP_NEXT (-2)   // the one after it (the extension that follows shade + connect)
+PLU_DEV int wave_vertex(const wave_buffers& wb, int b) {
+	if (b >= 0) return b;
+	return (int)wb.counters[(wb.desc->max_vertices + 1) * CNT_STRIDE] + (-1 - b);
+}
+
 #define PLU_CTA 256
 #ifndef PLU_ANYHIT
 #define PLU_ANYHIT 1   // 1: point-light shadow rays on the fast BVH stop at their first hit (k_connect)
@@ -136,19 +147,13 @@ extern __shared__ uint4 plu_smem[];
 
 // ---- k_generate -----------------------------------------------------------------------------------------------
 // stratified_sampler::generate_samples for one sample (sampler.h:58-69): stratum (s % n, s / n),
-// px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.
+// px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.  Only waves that extend with k_extend_pt
+// (fast BVH, persistent warps) start here; all others start with k_primary (k_extend<.., PRIMARY>).
+PLU_DEV ray primary_ray(const scene_ref& sc, const wave_desc& w, uint32_t slot);
 __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb) {
 	const wave_desc w = *wb.desc;
 	for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < w.n_slots; slot += gridDim.x * blockDim.x) {
-		philox_key key; int32_t px_x, px_y, s;
-		slot_to_path(w, slot, key, px_x, px_y, s);
-		u4 o = philox_call(key, 0u);
-		int32_t n = w.n_strata;
-		float dp = 1.f / (float)(uint32_t)n;
-		float sx = (float)(s % n), sy = (float)(s / n);
-		f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);
-		f2 lens = mk2((sx + u01(o.z) * 0.999f) * dp, (sy + u01(o.w) * 0.999f) * dp);
-		ray r = generate_ray(sc_in.cam, px, lens, w.use_lens != 0);
+		ray r = primary_ray(sc_in, w, slot);
 		wb.rec[4 * (size_t)slot] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
 		wb.rec[4 * (size_t)slot + 1] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
 		wb.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -192,15 +197,57 @@ PLU_DEV int extend_finish(const scene_ref& sc, float4* recs, float4* rad, int bo
 	return 0;
 }
 
+// stratified_sampler::generate_samples for one sample (sampler.h:58-69) + camera::generate_ray: the camera ray of a slot
+PLU_DEV ray primary_ray(const scene_ref& sc, const wave_desc& w, uint32_t slot) {
+	philox_key key; int32_t px_x, px_y, s;
+	slot_to_path(w, slot, key, px_x, px_y, s);
+	u4 o = philox_call(key, 0u);
+	int32_t n = w.n_strata;
+	float dp = 1.f / (float)(uint32_t)n;
+	float sx = (float)(s % n), sy = (float)(s / n);
+	f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);
+	f2 lens = mk2((sx + u01(o.z) * 0.999f) * dp, (sy + u01(o.w) * 0.999f) * dp);
+	return generate_ray(sc.cam, px, lens, w.use_lens != 0);
+}
+
+// extend_finish for the camera ray (k_primary): nothing of the path exists in memory yet, so a miss writes NOTHING
+// (renderer.cpp:61: `if (!scene->hit) return 0` — the slot's dirty bit stays 0 and k_accumulate adds 0 without
+// reading), an emissive hit writes L = 0 + 1 * Le, any other hit writes the whole 64-byte record and L = 0.
+PLU_DEV int primary_finish(const scene_ref& sc, float4* recs, float4* rad, uint32_t slot, const ray& r, bool hit, float t, int32_t prim, bool& dirty) {
+	dirty = hit;
+	if (!hit) return 0;
+	int4 meta = sc.prim_meta(prim);
+	int32_t mtag = sc.material(meta.y).tag;
+	if (mtag == PLU_MAT_EMISSION) {
+		hit_rec hr; fill_record(sc, prim, meta.x, r, t, false, hr);
+		f3 L = mk3(0.f) + mk3(1.f) * area_L(sc.light(meta.z), hr.norm, -r.d);
+		rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+		return 0;
+	}
+	float4* rec = recs + 4 * (size_t)slot;
+	rec[0] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
+	rec[1] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
+	rec[2] = make_float4(0.f, 0.f, 0.f, t);
+	rec[3] = make_float4(0.f, 0.f, 0.f, __int_as_float(prim));
+	rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+	return mtag == PLU_MAT_DIFFUSE ? 1 : 2;
+}
+
 // ---- k_extend -------------------------------------------------------------------------------------------------
+// PRIMARY (k_primary): the first kernel of a wave — camera ray generation fused into the extension of bounce 0.  The ray
+// of a slot is computed in registers and traced at once; it reaches memory only if it hits (k_generate + k_extend moved
+// 48 + 32 bytes per sample through HBM for rays of which, on the open scenes, three in four hit nothing).
 // Loop skeleton shared by extend / shade / connect: iteration i computes on rows that were gathered
 // into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
 // the queue entry of iteration i+2; queue pushes started in iteration i are completed in iteration i+1.
-template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
+template <bool SMEM, bool COUNT, bool PRIMARY = false>
+__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+	const int bounce = PRIMARY ? 0 : wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
+	wave_desc w;
+	if (PRIMARY) w = *wb.desc;
 	const uint32_t n = bounce == 0 ? wb.desc->n_slots : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	if (blockIdx.x * PLU_CTA >= n) return;   // a CTA without a first entry has no work: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
@@ -217,12 +264,13 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 
 	uint32_t j = blockIdx.x * PLU_CTA + tid;
 	uint32_t slot = 0, slot_next = 0;
-	if (j < n) {
+	if (!PRIMARY && j < n) {
 		slot = ident ? j : q[j];
 		cp_async_16(st_o + tid, recs + 4 * (size_t)slot); cp_async_16(st_d + tid, recs + 4 * (size_t)slot + 1);
 	}
 	cp_async_commit();
-	if (j + stride < n) slot_next = ident ? j + stride : q[j + stride];
+	if (PRIMARY) { slot = j; slot_next = j + stride; }
+	else if (j + stride < n) slot_next = ident ? j + stride : q[j + stride];
 	// Push state of one GROUP (see warp_tally): the whole CTA when the scene is staged in shared memory (uniform
 	// walk: every warp takes the same time, one barrier per iteration is free), a single warp otherwise
 	// (large scenes: r01f had 34 % of k_extend's stall samples on the CTA barrier, rays of different length).
@@ -242,16 +290,29 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
 		const uint32_t jn = j + stride, jnn = jn + stride;
 		const bool has_next = jn < n;
-		if (has_next) {
+		if (!PRIMARY && has_next) {
 			cp_async_16(st_o + (buf ^ 1u) * PLU_CTA + tid, recs + 4 * (size_t)slot_next);
 			cp_async_16(st_d + (buf ^ 1u) * PLU_CTA + tid, recs + 4 * (size_t)slot_next + 1);
 		}
-		cp_async_commit();
+		if (!PRIMARY) cp_async_commit();
 		uint32_t slot_nn = 0;
-		if (has_next && jnn < n) slot_nn = ident ? jnn : q[jnn];
-		cp_async_wait<1>();
+		if (PRIMARY) slot_nn = jnn;
+		else if (has_next && jnn < n) slot_nn = ident ? jnn : q[jnn];
+		if (!PRIMARY) cp_async_wait<1>();
 		bool active = j < n, to_diffuse = false, to_specular = false;
-		if (active) {
+		if (PRIMARY) {
+			bool dirty = false;
+			if (active) {
+				ray r = primary_ray(sc, w, slot);
+				float t; int32_t prim;
+				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
+				int cls = primary_finish(sc, recs, wb.rad, slot, r, hit, t, prim, dirty);
+				to_diffuse = cls == 1; to_specular = cls == 2;
+			}
+			// slots of a warp are 32 consecutive, 32-aligned indices: one mask word per warp and iteration
+			const uint32_t mask = __ballot_sync(0xffffffffu, dirty);
+			if (lane == 0 && j < n) wb.dirty[j >> 5] = mask;
+		} else if (active) {
 			float4 o = st_o[buf * PLU_CTA + tid], d = st_d[buf * PLU_CTA + tid];
 			ray r; r.e = mk3(o); r.d = mk3(d);
 			int flags = __float_as_int(d.w);
@@ -307,8 +368,9 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 #endif
 
 template <bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce, uint32_t refill) {
+__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
+	const int bounce = wave_vertex(wb, bounce_arg);
 	float4* const recs = wb.rec;
 	const bool ident = bounce == 0;
 	const uint32_t n = ident ? wb.desc->n_slots : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
@@ -385,7 +447,8 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+	const int bounce = wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	const wave_desc w = *wb.desc;
 	float4* const recs = wb.rec;
@@ -593,7 +656,8 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 // The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
 // `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce) {
+__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+	const int bounce = wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
 	unsigned char* stage_base = (unsigned char*)plu_smem;
@@ -670,6 +734,21 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 	}
 }
 
+// ---- k_loop_next ----------------------------------------------------------------------------------------------
+// Last node of the graph's while body: the extension of the next vertex has run; step the loop counter and decide whether
+// another round is needed.  No path is alive when that extension found no surface (its hit queues are empty): every later
+// launch of the wave would find empty queues, so the loop ends there (renderer.cpp:86-91: a miss ends the path).
+__global__ void k_loop_next(const __grid_constant__ wave_buffers wb, cudaGraphConditionalHandle handle) {
+	if (threadIdx.x != 0 || blockIdx.x != 0) return;
+	const int mv = wb.desc->max_vertices;
+	uint32_t* loop = wb.counters + (mv + 1) * CNT_STRIDE;
+	const uint32_t v = *loop + 1u;
+	*loop = v;
+	atomicAdd(wb.stats + 6, 1ull);   // rounds run: the host derives the launch count from it
+	const uint32_t hits = wb.counters[v * CNT_STRIDE + CNT_HIT_DIFFUSE] + wb.counters[v * CNT_STRIDE + CNT_HIT_SPECULAR];
+	cudaGraphSetConditional(handle, ((int)v < mv && hits > 0u) ? 1u : 0u);
+}
+
 // ---- k_accumulate ---------------------------------------------------------------------------------------------
 // target->pixel(floor(px)) += ray_color * smp_wgt, samples in ascending order (renderer.cpp:132).
 // The overflow-column strip (pixel index >= W*H, sampler.h:74-78) lands in pixel (0, row+1).
@@ -681,7 +760,10 @@ __global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave
 		float* o = fb + (size_t)dst * 3;
 		f3 acc = mk3(o[0], o[1], o[2]);
 		for (int32_t k = 0; k < w.kcount; ++k) {
-			f3 c = mk3(wb.rad[(size_t)k * (size_t)w.npix + q]);
+			const size_t slot = (size_t)k * (size_t)w.npix + q;
+			// a clean slot (camera ray missed, k_primary) holds L == 0: the add is done, the 16-byte read is not
+			const bool have = !w.use_dirty || ((wb.dirty[slot >> 5] >> (slot & 31u)) & 1u);
+			f3 c = have ? mk3(wb.rad[slot]) : mk3(0.f);
 			acc = acc + c * smp_wgt;
 		}
 		o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;

@@ -52,7 +52,7 @@ struct plu_gpu_ctx {
 	void* d_wave[PLU_PIPES] = {};
 	// One CUDA graph per pipe = the whole launch sequence of a wave (generate -> [extend, shade, shade, connect] x depth);
 	// valid while its key (scene tables, kernel variants, grids, buffers) is unchanged, see wave_graph_for()
-	struct wave_graph { cudaGraphExec_t exec = nullptr; std::vector<unsigned char> key; int launches = 0; };
+	struct wave_graph { cudaGraphExec_t exec = nullptr; std::vector<unsigned char> key; int launches = 0, body_launches = 0; bool looped = false; };
 	wave_graph graphs[PLU_PIPES];
 	wave_desc* h_descs = nullptr; size_t h_descs_cap = 0;   // pinned: the descriptors of a render's waves, copied to wb.desc wave by wave
 	int n_pipes = 4;                   // waves in flight (PLU_PIPES=1..4 overrides); 2 suffice for cornell-box, launch-bound scenes gain up to 4
@@ -64,7 +64,7 @@ struct plu_gpu_ctx {
 	std::vector<ncclComm_t> comms;
 	cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;   // around the framebuffer reduce
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-	cudaStream_t pipe[PLU_PIPES] = {};             // wave i of a render runs on pipe[i % n_pipes]; pipe[0] is unused (= the caller's stream)
+	cudaStream_t pipe[PLU_PIPES] = {};             // wave i of a render runs on pipe[i % n_pipes]: always the context's own streams (the caller's may be the legacy default stream, which cannot be captured into a graph); ordered against the caller's stream by events
 	cudaStream_t aux[PLU_PIPES] = {};              // per pipe: the specular shade kernel of a bounce runs beside the diffuse one
 	cudaEvent_t ev_fork[PLU_PIPES] = {}, ev_join[PLU_PIPES] = {};
 	cudaEvent_t ev_acc[PLU_PIPES] = {}, ev_start = nullptr;   // framebuffer adds stay in wave order
@@ -104,7 +104,7 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 		return PLU_E_CUDA;
 	}
 	for (int k = 0; k < PLU_PIPES; ++k) {
-		if ((k > 0 && (e = cudaStreamCreateWithFlags(&ctx->pipe[k], cudaStreamNonBlocking)) != cudaSuccess) ||
+		if ((e = cudaStreamCreateWithFlags(&ctx->pipe[k], cudaStreamNonBlocking)) != cudaSuccess ||
 		    (e = cudaStreamCreateWithFlags(&ctx->aux[k], cudaStreamNonBlocking)) != cudaSuccess ||
 		    (e = cudaEventCreateWithFlags(&ctx->ev_fork[k], cudaEventDisableTiming)) != cudaSuccess ||
 		    (e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess ||
@@ -460,13 +460,14 @@ static void select_bvh(const plu_gpu_ctx* ctx, scene_ref& sc, uint32_t flags) {
 #ifndef PLU_WAVE_PATHS
 #define PLU_WAVE_PATHS (1u << 22)
 #endif
+#define PLU_WAVE_PATHS_MAX (1u << 24)
 
 static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	if (ctx->cap[P] >= slots && ctx->d_wave[P]) return PLU_OK;
 	CU(cudaFree(ctx->d_wave[P])); ctx->d_wave[P] = nullptr; ctx->cap[P] = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long)) + al(sizeof(wave_desc));
+	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long)) + al(sizeof(wave_desc)) + al((N + 31) / 32 * 4);
 	CU(cudaMalloc(&ctx->d_wave[P], bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave[P];
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
@@ -480,6 +481,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
 	wb.desc = (const wave_desc*)take(sizeof(wave_desc));
+	wb.dirty = (uint32_t*)take((N + 31) / 32 * 4);
 	if ((size_t)(p - (unsigned char*)ctx->d_wave[P]) != bytes) return fail(ctx, PLU_E_NOMEM, "wave buffer carve-out mismatch");
 	ctx->cap[P] = slots;
 	return PLU_OK;
@@ -496,10 +498,15 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 }
 
 // dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
-struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_ext_pt, g_shade[2], g_conn, g_acc; };
+struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_prim, g_ext_pt, g_shade[2], g_conn, g_acc; };
+
+// Waves on the fast BVH of a sphere-free scene extend with persistent warps (k_extend_pt) and start with k_generate; all
+// other waves start with k_primary (camera ray generation fused into the first extension).
+static bool wave_uses_pt(const scene_ref& sc, const launch_cfg& c) { return !c.smem && sc.fast_nodes != nullptr && !sc.has_spheres && !c.no_pt; }
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
-	launch_cfg c; c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
+	launch_cfg c; std::memset(&c, 0, sizeof(c));   // (the struct is part of the graph key: no indeterminate padding)
+	c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
 	c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
 	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
@@ -510,6 +517,8 @@ static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
 	             : (count ? grid_for(ctx, K<false, true>, SM) : grid_for(ctx, K<false, false>, SM))
 	PICK(c.g_ext, k_extend, c.sm_ext); PICK(c.g_conn, k_connect, c.sm_conn);
 #undef PICK
+	c.g_prim = c.smem ? (count ? grid_for(ctx, k_extend<true, true, true>, c.sm_ext) : grid_for(ctx, k_extend<true, false, true>, c.sm_ext))
+	                  : (count ? grid_for(ctx, k_extend<false, true, true>, c.sm_ext) : grid_for(ctx, k_extend<false, false, true>, c.sm_ext));
 	c.g_shade[0] = c.smem ? grid_for(ctx, k_shade<true, CLS_DIFFUSE>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_DIFFUSE>, c.sm_shade);
 	c.g_shade[1] = c.smem ? grid_for(ctx, k_shade<true, CLS_SPECULAR>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_SPECULAR>, c.sm_shade);
 	return c;
@@ -537,60 +546,75 @@ struct wave_profiler {
 };
 
 // Enqueue one wave (generate -> [extend, shade, connect] x max_vertices); returns the launch count.
-// The wave's descriptor must already be on its way to wb.desc on `st` (put_desc); nothing here depends on the wave, so the
-// same sequence serves every wave of a render (and is what wave_graph_for captures).
-static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr, int P = 0) {
+// ---- launch sequence of a wave -----------------------------------------------------------------------------------
+// The wave's descriptor must already be on its way to wb.desc on `st` (put_desc); nothing below depends on the wave, so
+// the same sequence serves every wave of a render (and is what wave_graph_for records).  `b` is the path vertex, or
+// PLU_B_LOOP / PLU_B_LOOP_NEXT inside the graph's while loop (the kernels then read the vertex from device memory).
+static void launch_head(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, wave_profiler* pf, int P, bool pt) {
 	wave_buffers& wb = ctx->wbs[P];
-	wave_profiler none; if (!pf) pf = &none;
-	struct { int max_vertices; } w{max_vertices};
-	cudaMemsetAsync(wb.counters, 0, (size_t)(w.max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);
+	cudaMemsetAsync(wb.counters, 0, (size_t)(max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);   // incl. the loop word, row max_vertices + 1
 	pf->mark(-1, st);
-	k_generate<<<c.g_gen, 256, 0, st>>>(sc, wb);
-	pf->mark(0, st);
-	int launches = 1;
-	// the two shade kernels of a bounce touch disjoint slots and push through atomics: the specular one (few vertices,
+	if (pt) {
+		k_generate<<<c.g_gen, 256, 0, st>>>(sc, wb); pf->mark(0, st);
+		if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, 0, ctx->pt_refill);
+		else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, 0, ctx->pt_refill);
+	} else if (c.smem) {   // k_primary: generate + extend of vertex 0 in one kernel (its time is booked under "extend")
+		if (c.count) k_extend<true, true, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0); else k_extend<true, false, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0);
+	} else {
+		if (c.count) k_extend<false, true, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0); else k_extend<false, false, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0);
+	}
+	pf->mark(1, st);
+}
+
+static void launch_extend(plu_gpu_ctx* ctx, const scene_ref& sc, const launch_cfg& c, cudaStream_t st, wave_profiler* pf, int P, bool pt, int b) {
+	wave_buffers& wb = ctx->wbs[P];
+	if (pt) {   // fast BVH, no sphere (whose non-unit-direction rays need another walk): persistent warps with lane refill
+		if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+		else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+	} else if (c.smem) {
+		if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+		else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+	} else {
+		if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+		else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
+	}
+	pf->mark(1, st);
+}
+
+// shade (one kernel per material class) + connect of one vertex; returns the launch count
+static int launch_shade_connect(plu_gpu_ctx* ctx, const scene_ref& sc, const launch_cfg& c, cudaStream_t st, wave_profiler* pf, int P, int b) {
+	wave_buffers& wb = ctx->wbs[P];
+	// the two shade kernels of a vertex touch disjoint slots and push through atomics: the specular one (few vertices,
 	// mostly prologue and tail) runs on a second stream and fills the SMs the diffuse one leaves idle
 	const bool fork = ctx->has_specular && !pf->on && !c.no_fork;
-	for (int b = 0; b < w.max_vertices; ++b) {
-		if (c.smem) {
-			if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
-			else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
-			pf->mark(1, st);
-			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
-			k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
-			if (ctx->has_specular) {
-				cudaStream_t s2 = fork ? ctx->aux[P] : st;
-				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
-				k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b); launches++;
-				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
-			}
-			pf->mark(2, st);
-			if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
-			else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
-			pf->mark(3, st);
-		} else {
-			// fast BVH, no sphere (whose non-unit-direction rays need the reference tree): persistent warps with lane refill
-			const bool pt = sc.fast_nodes != nullptr && !sc.has_spheres && !c.no_pt;
-			if (pt) {
-				if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
-				else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
-			} else if (c.count) k_extend<false, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
-			else k_extend<false, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
-			pf->mark(1, st);
-			if (fork) cudaEventRecord(ctx->ev_fork[P], st);
-			k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
-			if (ctx->has_specular) {
-				cudaStream_t s2 = fork ? ctx->aux[P] : st;
-				if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
-				k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b); launches++;
-				if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
-			}
-			pf->mark(2, st);
-			if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
-			else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b);
-			pf->mark(3, st);
-		}
-		launches += 3;
+	int launches = 2;
+	if (fork) cudaEventRecord(ctx->ev_fork[P], st);
+	if (c.smem) k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
+	else k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
+	if (ctx->has_specular) {
+		cudaStream_t s2 = fork ? ctx->aux[P] : st;
+		if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
+		if (c.smem) k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b);
+		else k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b);
+		launches++;
+		if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
+	}
+	pf->mark(2, st);
+	if (c.smem) { if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	else { if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	pf->mark(3, st);
+	return launches;
+}
+
+// The whole chain, vertex by vertex (profiled renders, the parity hooks, and the fallback when graphs are unavailable).
+static int enqueue_wave(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, wave_profiler* pf = nullptr, int P = 0) {
+	wave_profiler none; if (!pf) pf = &none;
+	const bool pt = wave_uses_pt(sc, c);
+	launch_head(ctx, sc, max_vertices, c, st, pf, P, pt);
+	int launches = pt ? 2 : 1;
+	for (int b = 0; b < max_vertices; ++b) {
+		if (b > 0) { launch_extend(ctx, sc, c, st, pf, P, pt, b); launches++; }
+		launches += launch_shade_connect(ctx, sc, c, st, pf, P, b);
 	}
 	return launches;
 }
@@ -618,10 +642,58 @@ static plu_gpu_ctx::wave_graph* wave_graph_for(plu_gpu_ctx* ctx, const scene_ref
 	plu_gpu_ctx::wave_graph& g = ctx->graphs[P];
 	if (g.exec && g.key == key) return &g;
 	if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+	wave_profiler none;
+	const bool pt = wave_uses_pt(sc, c);
 	cudaGraph_t graph = nullptr;
+	cudaError_t e = cudaSuccess;
+	g.launches = 0; g.looped = false;
+	// measured (profiles/r02_summary.md): a round of the while loop costs more than the ~4 launches on empty queues it saves
+	// (glass0 16.8 looped vs 18.2 unrolled Gsamples/s, room 8.3 vs 8.5), so the loop is opt-in
+	static const bool no_loop = std::getenv("PLU_GRAPH_LOOP") == nullptr;
+	if (!no_loop) {
+		// memset -> first extension (k_primary | k_generate + k_extend_pt) -> WHILE { shade, connect of vertex v; extension of
+		// vertex v + 1; k_loop_next: ++v, go on iff v < max_vertices and the extension found a surface }: a wave stops at the
+		// depth its longest path reaches instead of running all 4 x max_vertices launches on empty queues
+		const cudaGraphNode_t* deps = nullptr; size_t ndeps = 0;
+		cudaStreamCaptureStatus cs; unsigned long long id; cudaGraph_t cg = nullptr;
+		cudaGraphConditionalHandle handle;
+		cudaGraphNode_t loop_node;
+		cudaGraphNodeParams cp = {};
+		const char* step = "cudaGraphCreate";
+		e = cudaGraphCreate(&graph, 0);
+		if (e == cudaSuccess) { step = "begin capture (head)"; e = cudaStreamBeginCaptureToGraph(st, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal); }
+		if (e == cudaSuccess) {
+			launch_head(ctx, sc, max_vertices, c, st, &none, P, pt);
+			step = "capture info"; e = cudaStreamGetCaptureInfo_v2(st, &cs, &id, &cg, &deps, &ndeps);
+			std::vector<cudaGraphNode_t> tail(deps, deps + (e == cudaSuccess ? ndeps : 0));
+			cudaGraph_t ended = nullptr;
+			cudaError_t e2 = cudaStreamEndCapture(st, &ended);
+			if (e == cudaSuccess && e2 != cudaSuccess) { step = "end capture (head)"; e = e2; }
+			if (e == cudaSuccess) { step = "conditional handle"; e = cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault); }
+			if (e == cudaSuccess) {
+				cp.type = cudaGraphNodeTypeConditional; cp.conditional.handle = handle; cp.conditional.type = cudaGraphCondTypeWhile; cp.conditional.size = 1;
+				step = "add while node"; e = cudaGraphAddNode(&loop_node, graph, tail.data(), tail.size(), &cp);
+			}
+			if (e == cudaSuccess) { step = "begin capture (body)"; e = cudaStreamBeginCaptureToGraph(st, cp.conditional.phGraph_out[0], nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal); }
+			if (e == cudaSuccess) {
+				int per_vertex = launch_shade_connect(ctx, sc, c, st, &none, P, PLU_B_LOOP);
+				launch_extend(ctx, sc, c, st, &none, P, pt, PLU_B_LOOP_NEXT);
+				k_loop_next<<<1, 32, 0, st>>>(ctx->wbs[P], handle);
+				step = "end capture (body)"; e = cudaStreamEndCapture(st, &ended);
+				g.launches = pt ? 2 : 1;            // the head; the rounds of the loop are counted on the device (stats[6])
+				g.body_launches = per_vertex + 2;
+			}
+		}
+		if (e == cudaSuccess) { step = "instantiate"; e = cudaGraphInstantiate(&g.exec, graph, 0); }
+		if (graph) cudaGraphDestroy(graph);
+		graph = nullptr;
+		if (e == cudaSuccess) { g.looped = true; g.key.swap(key); return &g; }
+		if (std::getenv("PLU_GRAPH_DEBUG")) std::fprintf(stderr, "libplugpu: looped wave graph unavailable (%s: %s), using the unrolled one\n", step, cudaGetErrorString(e));
+		cudaGetLastError(); g.exec = nullptr; g.body_launches = 0;   // fall through to the unrolled graph
+	}
 	if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return nullptr; }
 	g.launches = enqueue_wave(ctx, sc, max_vertices, c, st, nullptr, P);
-	cudaError_t e = cudaStreamEndCapture(st, &graph);
+	e = cudaStreamEndCapture(st, &graph);
 	if (e == cudaSuccess) e = cudaGraphInstantiate(&g.exec, graph, 0);
 	if (graph) cudaGraphDestroy(graph);
 	if (e != cudaSuccess) { cudaGetLastError(); g.exec = nullptr; return nullptr; }
@@ -671,15 +743,21 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	const int32_t spp = p->n_strata * p->n_strata;
 	const int32_t count = p->sample_count > 0 ? p->sample_count : spp;
 	const float smp_wgt = 1.f / (float)(uint32_t)spp;   // renderer.cpp:100
-	// paths per wave: a fixed default (PLU_WAVE_PATHS) or the caller's strata_per_wave — no state learnt from earlier
-	// renders: with one graph launch per wave the host cost per wave no longer depends on the path length
+	// Paths per wave: the caller's strata_per_wave, else 2^22 for the first waves and then a size DERIVED IN THIS CALL from
+	// what the first wave did (no state is kept between renders): a wave is a chain of ~4 dependent launches per path vertex
+	// whatever its size, so scenes whose paths are short (few rays per path: most launches of a wave nearly empty) run
+	// larger waves — glass0 18.2 -> 22.5, room 8.5 -> 9.2 Gsamples/s at 2^24; cornell-box (5.9 rays per path) stays at 2^22.
+	const bool adaptive = p->strata_per_wave <= 0 && std::getenv("PLU_NO_ADAPTIVE_WAVES") == nullptr;
 	uint32_t want = p->strata_per_wave > 0 ? (uint32_t)std::min<int64_t>(wh * p->strata_per_wave, (int64_t)1 << 26) : PLU_WAVE_PATHS;
 	want = (uint32_t)std::min<int64_t>(want, wh * (int64_t)count);
 	want = std::max<uint32_t>(want, (uint32_t)std::min<int64_t>(wh, 1 << 22));
-	rc = ensure_wave(ctx, want);
+	// buffers are sized for the largest wave this call may choose, so that growing the waves never allocates mid-render
+	uint32_t want_max = adaptive ? (uint32_t)std::max<int64_t>(want, std::min<int64_t>((int64_t)PLU_WAVE_PATHS_MAX, wh * (int64_t)count / 4)) : want;
+	rc = ensure_wave(ctx, want_max);
 	if (rc != PLU_OK) return rc;
 	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
 	cfg.no_pt = (p->flags & PLU_RENDER_NO_LANE_REFILL) != 0;
+	w.use_dirty = wave_uses_pt(sc, cfg) ? 0 : 1;
 	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
 	const bool use_graph = !prof.on && std::getenv("PLU_NO_GRAPH") == nullptr;
 	// Two waves in flight: even waves on the caller's stream, odd waves on ctx->pipe1 with the second buffer set.
@@ -687,48 +765,62 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	// independent waves the SMs one wave's kernel leaves idle at its tail (and between its launches) run the other
 	// wave's kernels.  The framebuffer adds stay in wave order (k_accumulate waits for its predecessor's event),
 	// so the image does not depend on the overlap.
-	const int64_t wcap = want;   // paths per wave of THIS render (the buffers may be larger from an earlier one)
+	int64_t wcap = want;   // paths per wave (the buffers may be larger)
 	const int64_t k_per_wave = std::max<int64_t>(1, wcap / std::min<int64_t>(wh, wcap));
 	const int64_t waves_total = ((wh + wcap - 1) / wcap) * ((count + k_per_wave - 1) / k_per_wave);
 	int NP = (prof.on || waves_total < 2) ? 1 : (int)std::min<int64_t>(ctx->n_pipes, waves_total);
 	for (int k = 1; k < NP; ++k)
-		if (ensure_wave(ctx, want, k) != PLU_OK) { cudaGetLastError(); NP = k; break; }   // no memory for another set: fewer waves in flight
+		if (ensure_wave(ctx, want_max, k) != PLU_OK) { cudaGetLastError(); NP = k; break; }   // no memory for another set: fewer waves in flight
 	const bool two = NP > 1;
 	rc = ensure_descs(ctx, (size_t)waves_total + (size_t)((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? (int64_t)count * ((p->height + wcap - 1) / wcap) : 0));
 	if (rc != PLU_OK) return rc;
 	for (int k = 0; k < NP; ++k) CU(cudaMemsetAsync(ctx->wbs[k].stats, 0, 8 * sizeof(unsigned long long), st));
 	CU(cudaEventRecord(ctx->ev0, st));
-	if (two) { CU(cudaEventRecord(ctx->ev_start, st)); for (int k = 1; k < NP; ++k) CU(cudaStreamWaitEvent(ctx->pipe[k], ctx->ev_start, 0)); }
-	uint64_t launches = 0, samples = 0, waves = 0;
+	CU(cudaEventRecord(ctx->ev_start, st));
+	for (int k = 0; k < NP; ++k) CU(cudaStreamWaitEvent(ctx->pipe[k], ctx->ev_start, 0));
+	uint64_t launches = 0, samples = 0, waves = 0, first_wave_samples = 1;
+	bool probe = adaptive && !prof.on && want_max > want && wh <= (int64_t)want;   // (images larger than a wave keep one size)
+	int body_launches = 0;   // launches per round of the graph loop (rounds are counted on the device)
 	// main image, then (compat) the overflow-column strip: sampler.h:74-78 renders x == W for rows 0..H-1
 	for (int pass = 0; pass < ((p->flags & PLU_RENDER_COMPAT_OVERFLOW_COLUMN) ? 2 : 1); ++pass) {
 		int64_t pbeg = pass == 0 ? 0 : wh, pend = pass == 0 ? wh : wh + p->height - 1;
 		for (int64_t p0 = pbeg; p0 < pend;) {
 			int64_t np = std::min<int64_t>(pend - p0, wcap);
-			int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, wcap / np));
+			int32_t K = 0;
 			for (int32_t k0 = 0; k0 < count; k0 += K) {
+				if (probe && waves == (uint64_t)NP) {   // NP waves keep the device busy while the first one's counters are read
+					probe = false;
+					unsigned long long h0[8];
+					CU(cudaEventSynchronize(ctx->ev_acc[0]));
+					CU(cudaMemcpyAsync(h0, ctx->wbs[0].stats, sizeof(h0), cudaMemcpyDeviceToHost, ctx->stream));
+					CU(cudaStreamSynchronize(ctx->stream));
+					const double r = (double)(h0[0] + h0[1]) / (double)first_wave_samples;   // rays per path
+					wcap = std::min<int64_t>(want_max, r < 2.0 ? (int64_t)want << 2 : (r < 3.5 ? (int64_t)want << 1 : (int64_t)want));
+				}
+				K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, wcap / np));
 				w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
 				w.n_slots = (uint32_t)(np * w.kcount);
 				const int P = (int)(waves % (uint64_t)NP);
-				cudaStream_t sp = P ? ctx->pipe[P] : st;
+				cudaStream_t sp = ctx->pipe[P];
 				if (waves >= ctx->h_descs_cap) return fail(ctx, PLU_E_NOMEM, "wave descriptor array too small");
 				ctx->h_descs[waves] = w;
 				rc = put_desc(ctx, ctx->h_descs + waves, sp, P);
 				if (rc != PLU_OK) return rc;
 				plu_gpu_ctx::wave_graph* wg = use_graph ? wave_graph_for(ctx, sc, w.max_vertices, cfg, sp, P) : nullptr;
-				if (wg) { CU(cudaGraphLaunch(wg->exec, sp)); launches += (uint64_t)wg->launches; }
+				if (wg) { CU(cudaGraphLaunch(wg->exec, sp)); launches += (uint64_t)wg->launches; body_launches = wg->body_launches; }
 				else launches += (uint64_t)enqueue_wave(ctx, sc, w.max_vertices, cfg, sp, &prof, P);
 				if (two && waves > 0) CU(cudaStreamWaitEvent(sp, ctx->ev_acc[(P + NP - 1) % NP], 0));   // the previous wave's add
 				k_accumulate<<<cfg.g_acc, 256, 0, sp>>>(w, ctx->wbs[P], d_rgb, smp_wgt);
-				if (two) CU(cudaEventRecord(ctx->ev_acc[P], sp));
-				prof.mark(4, st); prof.collect(st);
+				CU(cudaEventRecord(ctx->ev_acc[P], sp));
+				prof.mark(4, sp); prof.collect(sp);
 				launches++;
+				if (waves == 0) first_wave_samples = w.n_slots;
 				samples += w.n_slots; waves++;
 			}
 			p0 += np;
 		}
 	}
-	if (two && waves > 0 && ((waves - 1) % (uint64_t)NP) != 0) CU(cudaStreamWaitEvent(st, ctx->ev_acc[(waves - 1) % (uint64_t)NP], 0));   // the last add ran on another pipe
+	if (waves > 0) CU(cudaStreamWaitEvent(st, ctx->ev_acc[(waves - 1) % (uint64_t)NP], 0));   // the caller's stream resumes after the last add
 	CU(cudaEventRecord(ctx->ev1, st));
 	CU(cudaGetLastError());
 	CU(cudaStreamSynchronize(st));
@@ -741,7 +833,7 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 		float ms = 0.f; CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
 		stats->samples = samples; stats->rays_extend = h[0]; stats->rays_shadow = h[1];
 		stats->bvh_nodes_visited = h[2]; stats->prims_tested = h[3];
-		stats->ms_device = ms; stats->kernel_launches = launches;
+		stats->ms_device = ms; stats->kernel_launches = launches + h[6] * (uint64_t)body_launches;
 		stats->shade_vertices = h[4]; stats->shadow_entries = h[5]; stats->waves = waves;
 		stats->ms_generate = prof.ms[0]; stats->ms_extend = prof.ms[1]; stats->ms_shade = prof.ms[2];
 		stats->ms_connect = prof.ms[3]; stats->ms_accumulate = prof.ms[4];
@@ -919,7 +1011,8 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 	rc = ensure_wave(ctx, (uint32_t)std::min<int64_t>((int64_t)1 << 22, std::max<int64_t>(pixel_count, 1) * count));
 	if (rc != PLU_OK) return rc;
 	launch_cfg cfg = make_cfg(ctx, false);
-	std::vector<float4> host;
+	w.use_dirty = wave_uses_pt(sc, cfg) ? 0 : 1;
+	std::vector<float4> host; std::vector<uint32_t> dirty;
 	for (int64_t p0 = pixel_begin; p0 < pixel_begin + pixel_count;) {
 		int64_t np = std::min<int64_t>(pixel_begin + pixel_count - p0, ctx->cap[0]);
 		int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->cap[0] / np));
@@ -932,7 +1025,12 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 			CU(cudaGetLastError());
 			host.resize(w.n_slots);
 			CU(cudaMemcpyAsync(host.data(), ctx->wbs[0].rad, (size_t)w.n_slots * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+			if (w.use_dirty) {   // slots whose camera ray missed were never written: L == 0
+				dirty.resize(((size_t)w.n_slots + 31) / 32);
+				CU(cudaMemcpyAsync(dirty.data(), ctx->wbs[0].dirty, dirty.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			}
 			CU(cudaStreamSynchronize(ctx->stream));
+			if (w.use_dirty) for (size_t i = 0; i < (size_t)w.n_slots; ++i) if (!((dirty[i >> 5] >> (i & 31)) & 1u)) host[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 			for (int32_t k = 0; k < w.kcount; ++k)
 				for (int64_t q = 0; q < np; ++q) {
 					const float4& c = host[(size_t)k * (size_t)np + (size_t)q];

@@ -50,8 +50,33 @@ def run(ctx, sc, name, w, h, n, max_spp, steps=3, flags=0, spw=0):
             "mean_radiance": float(np.nanmean(img)), "nonfinite_pixels": int((~np.isfinite(img)).any(axis=2).sum())}
 
 
+def run_cold(sc, name, w, h, n, max_spp):
+    """First render of a scene on a FRESH context (nothing learnt, nothing allocated) against the second one:
+    wall clock around plu_gpu_render_device and the device-timed span."""
+    import time
+    import torch
+    from plutracer_b200 import GpuContext
+    spp = min(n * n, max_spp)
+    ctx = GpuContext(0)
+    ctx.upload(sc)
+    fb = torch.zeros(h, w, 3, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    st_ = torch.cuda.current_stream().cuda_stream
+    p = GpuContext.params(w, h, n, seed=20261104, sample_begin=0, sample_stride=1, sample_count=spp)
+    out = {"scene": name, "samples": w * h * spp}
+    for tag in ("first", "second", "third"):
+        t0 = time.perf_counter()
+        st = ctx.render_device(p, fb.data_ptr(), st_)
+        dt = time.perf_counter() - t0
+        out[tag] = {"wall_ms": dt * 1e3, "ms_device": st.ms_device, "msamples_per_s_device": st.samples / st.ms_device / 1e3,
+                    "msamples_per_s_wall": st.samples / dt / 1e6, "waves": int(st.waves), "launches": int(st.kernel_launches)}
+    ctx.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--cold", action="store_true", help="first vs second render on a fresh context per scene")
     ap.add_argument("--max-spp", type=int, default=256)
     ap.add_argument("--synth-n", type=int, default=1000000)
     ap.add_argument("--only", default="")
@@ -66,6 +91,9 @@ def main():
         if a.only and name not in a.only.split(","):
             continue
         sc = Scene.load_flat(os.path.join(ROOT, "tests", "golden", name + ".pluscene")).override(w, h, n)
+        if a.cold:
+            print(json.dumps(run_cold(sc, name, w, h, n, a.max_spp)), flush=True)
+            continue
         print(json.dumps(run(ctx, sc, name, w, h, n, a.max_spp, flags=flags, spw=a.strata_per_wave)), flush=True)
     if a.synth_n > 0 and (not a.only or "synth" in a.only):
         for kind in ("boxes", "mixed"):
