@@ -263,7 +263,9 @@ int plu_gpu_render_device(plu_gpu_ctx* ctx, const plu_render_params* p, float* d
  * scene->hit: per pixel the hit surface id (-1 = miss), t, and hit_record::norm.               */
 int plu_gpu_trace_primary(plu_gpu_ctx* ctx, int32_t width, int32_t height, uint32_t flags,
                           int32_t* surf_id, float* t, float* normal3);
-/* Arbitrary rays (o,d each n*3 float) through scene->hit.                                      */
+/* Arbitrary rays (o,d each n*3 float) through scene->hit.  With PLU_RENDER_COUNT_BVH in flags
+ * normal3 receives the cost of each ray's walk instead: (interior nodes visited, surfaces
+ * tested, 0) — diagnostics of the traversal structures.                                         */
 int plu_gpu_trace_rays(plu_gpu_ctx* ctx, int64_t n, const float* origin3, const float* dir3,
                        uint32_t flags, int32_t* surf_id, float* t, float* normal3);
 /* Per-sample radiance of ray_color for samples [sample_begin, +sample_count) of the pixels

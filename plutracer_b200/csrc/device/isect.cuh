@@ -422,13 +422,151 @@ PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t
 	return w.best >= 0;
 }
 
-// sphere::hit assumes a unit direction (sphere.cpp:17-19: b = -dot(v, d), det = b*b - dot(v, v) + r*r);
-// the reference also feeds it NON-unit directions (its shading frames are not orthonormal, Q9), for
-// which the quadratic accepts rays that miss the sphere's bounds — no geometric BVH can reproduce
-// that, so such rays take the reference's own tree whenever the scene has spheres.
+// ---- scenes with spheres: the walk that follows sphere::hit for ANY direction length ----------------------------
+// sphere::hit assumes a unit direction (sphere.cpp:17-19: b = -dot(v, d), det = b*b - dot(v, v) + r*r) but the reference
+// also feeds it NON-unit ones (its shading frames are not orthonormal, Q9).  With |d| = s, tau = the centre's offset along
+// the ray and rho its distance from the ray's axis, the quadratic accepts the sphere iff the origin is outside it,
+// tau > 0 and rho^2 <= r^2 + (s^2 - 1) tau^2: for s > 1 a CONE of half-angle atan(sqrt(s^2 - 1)) around the ray (spheres
+// far off the ray "hit"), for s < 1 an ellipsoid around the origin.  No geometric BVH describes that set, and which of
+// those spheres the reference finds also depends on ITS tree: a leaf is reached only through ancestors whose
+// origin-inflated boxes pass `tmax >= tmin` (bvh_tree.cpp:43-47), a real filter for hits that are not on the ray.
+//
+// trace_ref_pruned therefore walks the REFERENCE tree (same topology, same inflated boxes, same exact slab test, hence
+// the same reachable leaves) and adds to every interior node the TIGHT box of its surfaces (walk_node, built at upload)
+// to skip what cannot matter: a subtree is entered iff the reference enters it AND its tight box passes
+//   * the slab test against the ray (boxes, triangles: their tests are scale-invariant), or
+//   * the sphere criterion: the ray hits the box grown by the cone's width at the box's far end (general_walker),
+// and its lower bound of the hit distance does not exceed the best hit so far: the slab entry distance, or for spheres
+// i1 = b - sqrt(b^2 - q) = q / (b + sqrt(b^2 - q)) >= q / (2 b) >= (dist^2 - rmax^2) / (2 max w.d), q = |w|^2 - r^2.
+// Children are visited nearest bound first.  Candidates are tested with the unchanged sphere_t / box_t / triangle_t;
+// equal distances resolve to the later leaf in DFS order (bvh_tree.cpp:73).  Same (t, surface) as trace_ref, including
+// the rays the reference loses to its own inflated boxes (which a walk of the SAH tree cannot reproduce).
+struct general_walker {
+	f3 e, d, rrd, u;          // u = d / |d|
+	float s, g2;              // |d|;  max(|d|^2 - 1, 0) + margin: growth of the accepted radius^2 per unit of tau^2
+	float rmin, rmax2, best_t; int32_t best, best_rank;
+
+	PLU_DEV void begin(const ray& r, float rmin_, float rmax) {
+		e = r.e; d = r.d; rrd = 1.f / r.d;   // the value slabs() computes at every node (cmmn.h:155)
+		const float l2 = d.x * d.x + d.y * d.y + d.z * d.z;
+		s = sqrtf(l2);
+		// the reference evaluates det = b*b - dot(v,v) + r*r in float: its rounding (~1e-7 of b*b + |v|^2) acts like a
+		// direction that is up to ~2e-7 too long, so even "unit" rays get that much cone
+		g2 = fmaxf(l2 - 1.f, 0.f) + 5e-7f;
+		const float inv = 1.f / s;
+		u = mk3(d.x * inv, d.y * inv, d.z * inv);
+		rmin = rmin_; rmax2 = rmax < 0.f ? -1.f : rmax * rmax;
+		best_t = 0.f; best = -1; best_rank = -1;
+	}
+	// One tight box (lo, hi, rb = half its diagonal): lower bound of every acceptable hit distance inside it, or +inf when
+	// nothing in it can be accepted.  A sphere (c, r) is accepted only if the ray passes within R = sqrt(r^2 + g2 tau^2)
+	// of c at tau > 0, i.e. hits the sphere's own box c -+ r grown by R - r <= sqrt(rmin^2 + g2 tau_max^2) - rmin: ONE
+	// slab test on the grown box serves spheres (for |d| <= 1: no growth beyond the rounding margin), the plain one
+	// boxes and triangles.
+	PLU_DEV float child_key(float lx, float ly, float lz, float hx, float hy, float hz, float rb, float cull) const {
+		const float wlx = lx - e.x, wly = ly - e.y, wlz = lz - e.z, whx = hx - e.x, why = hy - e.y, whz = hz - e.z;
+		// slab test (boxes, triangles): entry / exit distance; NaN planes (0 * inf) drop out of fminf / fmaxf
+		const float ax = wlx * rrd.x, bx = whx * rrd.x, ay = wly * rrd.y, by = why * rrd.y, az = wlz * rrd.z, bz = whz * rrd.z;
+		const float n = fmax3f(fminf(ax, bx), fminf(ay, by), fminf(az, bz)), f = fmin3f(fmaxf(ax, bx), fmaxf(ay, by), fmaxf(az, bz));
+		float key = INFINITY;
+		if (!(f < n) && !(f < 0.f) && !(n > cull)) key = n;
+		if (rmax2 < 0.f) return key;   // no spheres in the scene
+		const float mx = 0.5f * (wlx + whx), my = 0.5f * (wly + why), mz = 0.5f * (wlz + whz);
+		const float tau = mx * u.x + my * u.y + mz * u.z;
+		const float t_hi = tau + rb, t_lo = tau - rb;   // range of tau over the centres in the box (via its bounding ball)
+		bool sph; float bmax = s * t_hi;
+		if (!(s > 0.f) || !(s < 3.0e38f)) { sph = true; bmax = 0.f; }   // zero / non-finite direction: no pruning
+		else if (!(t_hi > 0.f)) sph = false;                            // every centre lies behind the origin: b <= 0
+		else {
+			const float pad = (sqrtf(rmin * rmin + g2 * (t_hi * t_hi)) - rmin) * 1.01f + 1e-5f * (fabsf(t_hi) + rb);
+			const float px = pad * fabsf(rrd.x), py = pad * fabsf(rrd.y), pz = pad * fabsf(rrd.z);   // the grown box's planes move by pad / |d_k|
+			const float n2 = fmax3f(fminf(ax, bx) - px, fminf(ay, by) - py, fminf(az, bz) - pz);
+			const float f2 = fmin3f(fmaxf(ax, bx) + px, fmaxf(ay, by) + py, fmaxf(az, bz) + pz);
+			sph = !(f2 < n2) && !(f2 < 0.f);
+		}
+		if (sph) {
+			const float gx = fmaxf(fmaxf(wlx, -whx), 0.f), gy = fmaxf(fmaxf(wly, -why), 0.f), gz = fmaxf(fmaxf(wlz, -whz), 0.f);
+			const float q = gx * gx + gy * gy + gz * gz - rmax2;   // <= |w|^2 - r^2 of every sphere in the box
+			float lb = (q > 0.f && bmax > 0.f) ? (q / (2.f * bmax)) * 0.999f : 0.f;   // i1 = q / (b + sqrt(b^2 - q)) >= q / (2 b)
+			// and, i1 growing with rho, i1 >= s tau - sqrt((s^2 - 1) tau^2 + r^2), which itself grows with tau: the value at t_lo
+			if (t_lo > 0.f) lb = fmaxf(lb, (s * t_lo - sqrtf(g2 * (t_lo * t_lo) + rmax2)) * 0.999f - 1e-5f * t_lo);
+			if (!(lb == lb)) lb = 0.f;
+			if (!(lb > cull)) key = fminf(key, lb);
+		}
+		return key;
+	}
+};
+
+template <bool COUNT, int S>
+PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
+	const walk_node* nodes = sc.walk_nodes;
+	general_walker w;
+	w.begin(r, sc.sphere_rmin, sc.has_spheres ? sc.sphere_rmax : -1.f);
+	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
+	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
+	int sp = 0;
+	// one child of an interior node: a leaf is tested at once (the reference tests leaves without a box, bvh_tree.cpp:40),
+	// an interior child yields its key (+inf: the reference does not enter it, or nothing in it can improve the result)
+	auto visit = [&](int32_t node, int32_t k, float cull) -> float {
+		const walk_node* nd = nodes + node;
+		const float4 a = __ldg(&nd->a), b = __ldg(&nd->b);
+		if (k == 1) {
+			const int32_t tag = __float_as_int(a.w), prim = __float_as_int(b.w);
+			float t; bool h;
+			if (COUNT) tc->prims++;
+			if (tag == PLU_PRIM_BOX) h = box_t(a, b, r, PLU_T_MAX, t);
+			else if (tag == PLU_PRIM_SPHERE) h = sphere_t(make_float4(a.x, a.y, a.z, b.x), r, PLU_T_MAX, t);
+			else { const float4* p = sc.prim(prim); h = triangle_t(__ldg(p), __ldg(p + 1), __ldg(p + 2), r, PLU_T_MAX, t); }
+			if (h) {
+				const int32_t rank = __float_as_int(__ldg(&nd->d).w);
+				if (w.best < 0 || t < w.best_t || (t == w.best_t && rank > w.best_rank)) { w.best_t = t; w.best = prim; w.best_rank = rank; }
+			}
+			return INFINITY;
+		}
+		float tmin, tmax; slabs_rrd(mk3(a), mk3(b), r.e, w.rrd, tmin, tmax);   // the reference's own test on its own box
+		if (!(tmax >= tmin)) return INFINITY;
+		const float4 c = __ldg(&nd->c), d = __ldg(&nd->d);
+		return w.child_key(c.x, c.y, c.z, d.x, d.y, d.z, d.w, cull);
+	};
+	int32_t cur = 0;
+	if (sc.n_prims == 1) { visit(0, 1, 3.0e38f); cur = -1; }
+	else {   // the root is tested like any interior node
+		float tmin, tmax; const walk_node* nd = nodes;
+		slabs_rrd(mk3(__ldg(&nd->a)), mk3(__ldg(&nd->b)), r.e, w.rrd, tmin, tmax);
+		if (!(tmax >= tmin)) cur = -1;
+	}
+	while (cur >= 0) {
+		const int32_t k = __float_as_int(__ldg(&nodes[cur].c).w);
+		const int32_t kl = k >> 1, L = cur + 1, R = cur + 2 * kl;
+		if (COUNT) tc->nodes++;
+		float cull = w.best >= 0 ? w.best_t + fabsf(w.best_t) * 1e-5f : 3.0e38f;
+		const float k0 = visit(L, kl, cull);
+		if (w.best >= 0) cull = w.best_t + fabsf(w.best_t) * 1e-5f;
+		const float k1 = visit(R, k - kl, cull);
+		if (any_hit && w.best >= 0) break;
+		const bool h0 = k0 < INFINITY, h1 = k1 < INFINITY;
+		if (h0 && h1) {
+			const bool first1 = k1 < k0;
+			stack.push(sp++, first1 ? L : R);
+			cur = first1 ? R : L;
+		} else if (h0) cur = L;
+		else if (h1) cur = R;
+		else {
+			// a stacked subtree may have fallen behind the best hit found since it was pushed: its key is re-derived on
+			// expansion (visit() of its children), so popping it unconditionally only costs those two visits
+			if (sp > 0) cur = stack.pop(--sp); else cur = -1;
+		}
+	}
+	t_out = w.best_t; prim_out = w.best;
+	return w.best >= 0;
+}
+
 template <bool COUNT, bool SMEM>
 PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc, bool any_hit = false) {
-	if (sc.fast_nodes != nullptr && (!sc.has_spheres || fabsf(dot(r.d, r.d) - 1.f) <= 1e-5f)) return trace_fast<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+	if (sc.fast_nodes != nullptr) {
+		if (sc.has_spheres) return trace_ref_pruned<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+		return trace_fast<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+	}
 	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT, SMEM>(sc, r, root_bound, t, prim, tc);
 	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);
 }

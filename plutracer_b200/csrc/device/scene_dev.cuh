@@ -37,6 +37,15 @@ struct fast_node { float4 a, b, c; int4 d; };
 struct wide_node { float4 lox, loy, loz, hix, hiy, hiz; int4 ref; int4 pad; };
 #define PLU_WIDE_EMPTY ((int32_t)0x80000000)
 
+// Node of the pruned reference-tree walk (scenes with spheres, isect.cuh: trace_ref_pruned), 64 B, same pre-order index
+// space as ref_node:
+//   interior  a = ref lo | skip     b = ref hi | -1      c = tight min | leaf count k (int)   d = tight max | half diagonal
+//   leaf      a = ref lo | kind     b = ref hi | surface c = - | 1                            d = - | DFS rank (tie rule)
+// (tight = padded union of the subtree's surface bounds; ref lo/hi = the reference's origin-inflated box, for a sphere
+// leaf centre / radius as in ref_node).  Children of interior node i with k leaves: i + 1 (k / 2 leaves) and
+// i + 2 * (k / 2) (the rest) — the tree's shape is a function of the surface count alone (bvh_tree.cpp:27-31).
+struct walk_node { float4 a, b, c, d; };
+
 struct scene_ref {
 	const unsigned char* blob;      // base (global, or shared after staging)
 	uint32_t blob_bytes;
@@ -50,8 +59,10 @@ struct scene_ref {
 	const int32_t* fast_prim_index; // leaf slots -> prim ids
 	const float4* fast_leaf;        // leaf slots -> surface records (see fast_node)
 	const wide_node* wide_nodes;    // null: walk fast_nodes two children at a time
+	const walk_node* walk_nodes;    // non-null: scenes with spheres walk the reference tree with tight-box pruning
 	int32_t n_fast_nodes;
 	int32_t has_spheres;
+	float sphere_rmax, sphere_rmin; // largest / smallest sphere radius of the scene (trace_ref_pruned's node criterion)
 	plu_camera_desc cam;
 
 	PLU_DEV const ref_node* ref_nodes() const { return (const ref_node*)(blob + off_ref_nodes); }

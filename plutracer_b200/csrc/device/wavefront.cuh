@@ -772,7 +772,7 @@ __global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave
 
 // ---- parity hooks ---------------------------------------------------------------------------------------------
 // scene->hit for explicit rays: surface id, t, hit_record::norm.
-template <bool SMEM>
+template <bool SMEM, bool COUNT = false>
 __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ scene_ref sc_in, int64_t n, const float* o3, const float* d3,
                                                     int primary_w, int primary_h, int32_t* id, float* t_out, float* n3) {
 	scene_ref sc = sc_in;
@@ -785,11 +785,12 @@ __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ scen
 		} else {
 			r.e = mk3(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2]); r.d = mk3(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2]);
 		}
-		float t; int32_t prim; trace_counts tc;
-		if (trace_scene<false, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc)) {
+		float t; int32_t prim; trace_counts tc; tc.nodes = 0; tc.prims = 0;
+		if (trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc)) {
 			hit_rec hr; fill_record(sc, prim, sc.prim_meta(prim).x, r, t, false, hr);
 			id[i] = prim; t_out[i] = t; n3[3 * i] = hr.norm.x; n3[3 * i + 1] = hr.norm.y; n3[3 * i + 2] = hr.norm.z;
 		} else { id[i] = -1; t_out[i] = 0.f; n3[3 * i] = 0.f; n3[3 * i + 1] = 0.f; n3[3 * i + 2] = 0.f; }
+		if (COUNT) { n3[3 * i] = (float)tc.nodes; n3[3 * i + 1] = (float)tc.prims; n3[3 * i + 2] = 0.f; }   // the walk's cost instead of the normal
 	}
 }
 

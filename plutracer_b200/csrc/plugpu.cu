@@ -13,6 +13,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -40,6 +41,7 @@ struct plu_gpu_ctx {
 	float *d_tri_uv = nullptr, *d_tri_normal = nullptr, *d_texels = nullptr;
 	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr; float4* d_fast_leaf = nullptr;
 	wide_node* d_wide = nullptr;   // PLU_WIDE=1: four-child nodes collapsed from d_fast (k_collapse_wide)
+	walk_node* d_walk = nullptr;   // scenes with spheres on the fast path: the reference tree with tight boxes (trace_ref_pruned)
 	bool blob_in_smem = false;
 	bool use_fast = false;
 	bool has_specular = false;     // any perfect-reflection / perfect-refraction / glass material
@@ -194,6 +196,7 @@ extern "C" int plu_gpu_device_count(const plu_gpu_ctx* ctx) { return ctx ? 1 + (
 static void free_scene(plu_gpu_ctx* ctx) {
 	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
 	cudaFree(ctx->d_wide); ctx->d_wide = nullptr;
+	cudaFree(ctx->d_walk); ctx->d_walk = nullptr;
 	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index); cudaFree(ctx->d_fast_leaf); ctx->d_fast_leaf = nullptr;
 	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
 	ctx->have_scene = false;
@@ -277,6 +280,59 @@ static int upload_single(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t bui
 
 // A multi-device context deep-copies the scene to every device and builds the traversal structures on each (one host
 // thread per device; the builds are deterministic, so all devices hold byte-identical tables).
+// ---- walk_node table of trace_ref_pruned (scene_dev.cuh): the reference tree + the tight box of every subtree ----
+// float <-> unsigned images that keep the order, so that boxes merge with atomicMin / atomicMax
+__device__ __forceinline__ uint32_t f2ord(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__device__ __forceinline__ float ord2f(uint32_t u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+
+__global__ void k_walk_init(int32_t n_nodes, const ref_node* ref, walk_node* out) {
+	const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_nodes) return;
+	const uint32_t pinf = f2ord(INFINITY), ninf = f2ord(-INFINITY);
+	walk_node w; w.a = ref[i].lo; w.b = ref[i].hi;
+	w.c = make_float4(__uint_as_float(pinf), __uint_as_float(pinf), __uint_as_float(pinf), __int_as_float(1));
+	w.d = make_float4(__uint_as_float(ninf), __uint_as_float(ninf), __uint_as_float(ninf), __int_as_float(0));
+	out[i] = w;
+}
+// one thread per surface: its padded tight box joins every ancestor on the way from the root to its leaf (the path
+// follows from the leaf's DFS rank: left subtree = the first k / 2 leaves)
+__global__ void k_walk_merge(int32_t n, const float* prim, const int32_t* meta, walk_node* out) {
+	const int32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n) return;
+	const float* f = prim + (size_t)s * 12;
+	const int32_t tag = meta[4 * s], rank = meta[4 * s + 3];
+	float mn[3], mx[3];
+	for (int i = 0; i < 3; ++i) {
+		if (tag == PLU_PRIM_SPHERE) { mn[i] = f[i] - fabsf(f[3]); mx[i] = f[i] + fabsf(f[3]); }
+		else if (tag == PLU_PRIM_BOX) { mn[i] = fminf(f[i], f[4 + i]); mx[i] = fmaxf(f[i], f[4 + i]); }
+		else { mn[i] = fminf(f[i], fminf(f[4 + i], f[8 + i])); mx[i] = fmaxf(f[i], fmaxf(f[4 + i], f[8 + i])); }
+	}
+	float big = 0.f, diag = 0.f;
+	for (int i = 0; i < 3; ++i) { big = fmaxf(big, fmaxf(fabsf(mn[i]), fabsf(mx[i]))); diag += mx[i] - mn[i]; }
+	const float pad = 1e-5f * big + 1e-5f * diag + 1e-30f;   // guard band >> rounding of the slab / hit arithmetic (as the fast BVH)
+	int32_t node = 0, lo = 0, k = n;
+	while (k > 1) {
+		uint32_t* c = (uint32_t*)&out[node].c; uint32_t* d = (uint32_t*)&out[node].d;
+		for (int i = 0; i < 3; ++i) { atomicMin(c + i, f2ord(mn[i] - pad)); atomicMax(d + i, f2ord(mx[i] + pad)); }
+		((int32_t*)c)[3] = k;   // every surface below writes the same value
+		const int32_t half = k / 2;
+		if (rank < lo + half) { node += 1; k = half; } else { node += 2 * half; lo += half; k -= half; }
+	}
+	((int32_t*)&out[node].c)[3] = 1;
+	((int32_t*)&out[node].d)[3] = rank;
+}
+__global__ void k_walk_finish(int32_t n_nodes, walk_node* out) {
+	const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_nodes) return;
+	if (__float_as_int(out[i].b.w) >= 0) return;   // leaf
+	float4 c = out[i].c, d = out[i].d;
+	c.x = ord2f(__float_as_uint(c.x)); c.y = ord2f(__float_as_uint(c.y)); c.z = ord2f(__float_as_uint(c.z));
+	d.x = ord2f(__float_as_uint(d.x)); d.y = ord2f(__float_as_uint(d.y)); d.z = ord2f(__float_as_uint(d.z));
+	const float ex = d.x - c.x, ey = d.y - c.y, ez = d.z - c.z;
+	d.w = 0.5f * sqrtf(ex * ex + ey * ey + ez * ez) * 1.0001f;   // radius of the box's bounding ball (trace_ref_pruned)
+	out[i].c = c; out[i].d = d;
+}
+
 extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
 	if (ctx->peers.empty()) return upload_single(ctx, d, build, stats);
@@ -346,7 +402,12 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 	sc.n_ref_nodes = (int32_t)ref_nodes.size();
 	sc.n_prims = d->n_prims; sc.n_materials = d->n_materials; sc.n_textures = d->n_textures; sc.n_lights = d->n_lights;
 	sc.cam = d->cam;
-	for (size_t s = 0; s < n; ++s) if (d->prim_tag[s] == PLU_PRIM_SPHERE) sc.has_spheres = 1;
+	sc.sphere_rmin = 3.0e38f;
+	for (size_t s = 0; s < n; ++s) if (d->prim_tag[s] == PLU_PRIM_SPHERE) {
+		const float r = std::fabs(d->prim_data[12 * s + 3]);
+		sc.has_spheres = 1; sc.sphere_rmax = std::max(sc.sphere_rmax, r); sc.sphere_rmin = std::min(sc.sphere_rmin, r);
+	}
+	if (!sc.has_spheres) sc.sphere_rmin = 0.f;
 	CU(cudaMalloc(&ctx->d_blob, blob.size()));
 	CU(cudaMemcpy(ctx->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
 	sc.blob = ctx->d_blob;
@@ -420,6 +481,19 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 		CU(cudaGetLastError());
 		CU(cudaStreamSynchronize(ctx->stream));
 		sc.wide_nodes = ctx->d_wide;
+	}
+	sc.walk_nodes = nullptr;
+	if (sc.has_spheres && sc.n_ref_nodes > 0) {   // (small scenes only reach it with PLU_RENDER_BVH_FAST)
+		// sphere::hit is fed non-unit directions, which no walk of the SAH tree can follow: those scenes walk the reference
+		// tree with tight-box pruning instead (isect.cuh: trace_ref_pruned)
+		CU(cudaMalloc(&ctx->d_walk, (size_t)sc.n_ref_nodes * sizeof(walk_node)));
+		const int nb = (sc.n_ref_nodes + 255) / 256;
+		k_walk_init<<<nb, 256, 0, ctx->stream>>>(sc.n_ref_nodes, (const ref_node*)(ctx->d_blob + sc.off_ref_nodes), ctx->d_walk);
+		k_walk_merge<<<(sc.n_prims + 255) / 256, 256, 0, ctx->stream>>>(sc.n_prims, (const float*)(ctx->d_blob + sc.off_prim), (const int32_t*)(ctx->d_blob + sc.off_prim_meta), ctx->d_walk);
+		k_walk_finish<<<nb, 256, 0, ctx->stream>>>(sc.n_ref_nodes, ctx->d_walk);
+		CU(cudaGetLastError());
+		CU(cudaStreamSynchronize(ctx->stream));
+		sc.walk_nodes = ctx->d_walk;
 	}
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
@@ -649,7 +723,7 @@ static plu_gpu_ctx::wave_graph* wave_graph_for(plu_gpu_ctx* ctx, const scene_ref
 	g.launches = 0; g.looped = false;
 	// measured (profiles/r02_summary.md): a round of the while loop costs more than the ~4 launches on empty queues it saves
 	// (glass0 16.8 looped vs 18.2 unrolled Gsamples/s, room 8.3 vs 8.5), so the loop is opt-in
-	static const bool no_loop = std::getenv("PLU_GRAPH_LOOP") == nullptr;
+	const bool no_loop = std::getenv("PLU_GRAPH_LOOP") == nullptr;
 	if (!no_loop) {
 		// memset -> first extension (k_primary | k_generate + k_extend_pt) -> WHILE { shade, connect of vertex v; extension of
 		// vertex v + 1; k_loop_next: ++v, go on iff v < max_vertices and the extension found a surface }: a wave stops at the
@@ -972,7 +1046,10 @@ static int trace_common(plu_gpu_ctx* ctx, int64_t n, const float* o3, const floa
 	}
 	CUX(cudaMalloc(&d_id, (size_t)n * 4)); CUX(cudaMalloc(&d_t, (size_t)n * 4)); CUX(cudaMalloc(&d_n, (size_t)n * 12));
 	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
-	if (ctx->blob_in_smem) k_trace_rays<true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+	if (flags & PLU_RENDER_COUNT_BVH) {
+		if (ctx->blob_in_smem) k_trace_rays<true, true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+		else k_trace_rays<false, true><<<grid, 256, 0, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+	} else if (ctx->blob_in_smem) k_trace_rays<true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
 	else k_trace_rays<false><<<grid, 256, 0, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
 	CUX(cudaGetLastError());
 	CUX(cudaMemcpyAsync(surf_id, d_id, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));

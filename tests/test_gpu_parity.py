@@ -303,3 +303,102 @@ def test_waves_in_flight_do_not_change_the_image(lib, name, monkeypatch):
             ctx.close()
     assert same_bits(imgs[0], imgs[1]).all() and same_bits(imgs[0], imgs[2]).all()
     assert np.nansum(imgs[0]) > 0.25 * imgs[0].size
+
+
+# ---- scenes with spheres on the fast BVH: sphere::hit is fed non-unit directions (SURVEY.md 8d config 5 as worded) ----
+@pytest.fixture(scope="module")
+def synth_spheres():
+    from tools.gen_synth import make_scene
+    return make_scene(20000, seed=4, kind="spheres", width=160, height=160, n_strata=2)
+
+
+def _sphere_rays(rng, n, extent):
+    """origins in and around the lattice; unit, shortened (|d| 0.2..1) and stretched (|d| 1..2.5) directions"""
+    ro = rng.uniform(-extent, extent, (n, 3)).astype(np.float32)
+    rd = rng.normal(size=(n, 3)).astype(np.float32)
+    rd /= np.linalg.norm(rd, axis=1, keepdims=True)
+    k = n // 5
+    rd[k:2 * k] *= rng.uniform(0.2, 1.0, (k, 1)).astype(np.float32)
+    rd[2 * k:4 * k] *= rng.uniform(1.0, 2.5, (2 * k, 1)).astype(np.float32)
+    rd[4 * k:4 * k + k // 2] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, k // 2)] * rng.uniform(0.3, 2.0, (k // 2, 1)).astype(np.float32)
+    return ro, rd
+
+
+def test_sphere_scene_general_walk_equals_reference_tree_on_rays(gpu, oracle, synth_spheres):
+    """20 002 surfaces, 20 000 of them spheres: the pruned walk (cone criterion + reference ancestor check) against the
+    exhaustive walk of the reference's own tree, bit-exact (id, t, normal), on 100 000 rays of which 80 % are non-unit
+    (for |d| > 1 sphere::hit accepts spheres far off the ray; for |d| < 1 it misses spheres the ray goes through)."""
+    gpu.upload(synth_spheres)
+    rng = np.random.default_rng(21)
+    ro, rd = _sphere_rays(rng, 100000, 60.0)
+    x = gpu.trace_rays(ro, rd, REF)
+    y = gpu.trace_rays(ro, rd, 0)
+    keep = ~oracle.nan_slab_rays(synth_spheres, ro, rd)
+    assert keep.mean() > 0.99
+    hit = x[0] >= 0
+    assert 0.2 < hit.mean() < 0.999
+    # stretched directions really do "hit" spheres the ray misses geometrically (what the pruned walk has to follow)
+    assert np.array_equal(x[0][keep], y[0][keep]) and same_bits(x[1][keep], y[1][keep]).all() and same_bits(x[2][keep], y[2][keep]).all()
+    ids, t, n = oracle.trace_rays(synth_spheres, ro[:2000], rd[:2000])
+    assert np.array_equal(ids, y[0][:2000]) and same_bits(t, y[1][:2000]).all()
+    # primary rays
+    a, b = gpu.trace_primary(160, 160, REF), gpu.trace_primary(160, 160, 0)
+    assert np.array_equal(a[0], b[0]) and same_bits(a[1], b[1]).all() and (a[0] >= 0).mean() > 0.3
+
+
+def test_sphere_scene_full_paths_equal_reference_tree(gpu, oracle, synth_spheres):
+    from plutracer_b200 import GpuContext
+    gpu.upload(synth_spheres)
+    w, h, n = 160, 160, 2
+    first = 160 * 70
+    a = gpu.sample_radiance(GpuContext.params(w, h, n, seed=13, flags=REF), first, 160 * 8)
+    b = gpu.sample_radiance(GpuContext.params(w, h, n, seed=13), first, 160 * 8)
+    assert same_bits(a, b).all() and np.nansum(a) > 0
+    want = oracle.sample_radiance(synth_spheres, GpuContext.params(w, h, n, seed=13), first, 64, trig=0)
+    assert same_bits(b[:64], want).all()
+    img_ref, img = np.zeros((h, w, 3), np.float32), np.zeros((h, w, 3), np.float32)
+    s1 = gpu.render(GpuContext.params(w, h, n, seed=13, flags=REF), img_ref)
+    s2 = gpu.render(GpuContext.params(w, h, n, seed=13), img)
+    assert same_bits(img_ref, img).all()
+    assert (s1.rays_extend, s1.rays_shadow, s1.shade_vertices) == (s2.rays_extend, s2.rays_shadow, s2.shade_vertices)
+
+
+def test_sphere_scene_200k_rays(gpu, oracle):
+    """200 002 surfaces (the size at which the exhaustive walk visited 5453 nodes per ray): 20 000 rays, both walks."""
+    from tools.gen_synth import make_scene
+    sc = make_scene(200000, seed=5, kind="spheres", width=64, height=64, n_strata=1)
+    gpu.upload(sc)
+    rng = np.random.default_rng(22)
+    ro, rd = _sphere_rays(rng, 20000, 60.0)
+    x = gpu.trace_rays(ro, rd, REF)
+    y = gpu.trace_rays(ro, rd, 0)
+    keep = ~oracle.nan_slab_rays(sc, ro, rd)
+    assert np.array_equal(x[0][keep], y[0][keep]) and same_bits(x[1][keep], y[1][keep]).all()
+    assert (x[0] >= 0).mean() > 0.2
+
+
+@pytest.mark.parametrize("name", ["glass0", "room"])
+def test_graph_replay_and_wave_size_do_not_change_the_image(lib, name, monkeypatch):
+    """One CUDA graph launch per wave (default), the while-loop graph (PLU_GRAPH_LOOP), direct launches (PLU_NO_GRAPH),
+    fixed and in-call adapted wave sizes: bit-identical images and identical ray counts."""
+    from plutracer_b200 import GpuContext
+    w, h, n = 640, 480, 16   # 256 strata x 307 200 pixels = 78.6 M paths: 20 waves of 2^22, fewer once the probe enlarges them
+    sc = golden_scene(name, w, h, n)
+    out = []
+    for env in ({}, {"PLU_GRAPH_LOOP": "1"}, {"PLU_NO_GRAPH": "1"}, {"PLU_NO_ADAPTIVE_WAVES": "1"}):
+        for k in ("PLU_GRAPH_LOOP", "PLU_NO_GRAPH", "PLU_NO_ADAPTIVE_WAVES"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        ctx = GpuContext(0)
+        try:
+            ctx.upload(sc)
+            img = np.full((h, w, 3), 0.5, np.float32)
+            st = ctx.render(GpuContext.params(w, h, n, seed=17), img)
+            out.append((img, st))
+        finally:
+            ctx.close()
+    for img, st in out[1:]:
+        assert same_bits(out[0][0], img).all()
+        assert (st.samples, st.rays_extend, st.rays_shadow, st.shade_vertices) == (out[0][1].samples, out[0][1].rays_extend, out[0][1].rays_shadow, out[0][1].shade_vertices)
+    assert out[0][1].waves < out[3][1].waves   # the adapted render used larger waves
