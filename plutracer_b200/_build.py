@@ -20,7 +20,6 @@ NVCC_FLAGS = [
     *(["-DPLU_LEAF_SMALL=" + os.environ["PLU_LEAF_SMALL"]] if os.environ.get("PLU_LEAF_SMALL") else []),
     *(["-DPLU_SSTK=" + os.environ["PLU_SSTK"]] if os.environ.get("PLU_SSTK") else []),
     *(["-DPLU_ANYHIT=" + os.environ["PLU_ANYHIT"]] if os.environ.get("PLU_ANYHIT") else []),
-    *(["-DPLU_WIDE_WALK=" + os.environ["PLU_WIDE_WALK"]] if os.environ.get("PLU_WIDE_WALK") else []),
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread", "-shared",
 ]
 

@@ -281,13 +281,14 @@ PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, 
 #ifndef PLU_SSTK
 #define PLU_SSTK 8
 #endif
-#ifndef PLU_WIDE_WALK
-#define PLU_WIDE_WALK 0   // 1: compile the four-child walk (node_step_wide); it runs when the scene was uploaded with PLU_WIDE=1
-#endif
 #define PLU_WALK_CTA 256   // == PLU_CTA and k_trace_rays' block size
+// Capacity: both builders split by SAH down to depth 40 and halve the surface count from there on (host/bvh_build.cpp,
+// bvh_gpu.cu), so a tree over n surfaces is at most 41 + ceil(log2 n) <= PLU_WALK_DEPTH_MAX levels deep for every int32
+// n, and the walks push at most one entry per level; plu_gpu_upload_scene re-checks the bound against the built tree.
+#define PLU_WALK_DEPTH_MAX 72
 template <int S> struct walk_stack {
 	int32_t* sm;        // &shared[0][threadIdx.x] (unused when S == 0)
-	int32_t loc[96];    // host/bvh_build.cpp bounds the tree depth to 60 (wide walk: <= 3 pushes per two levels)
+	int32_t loc[PLU_WALK_DEPTH_MAX - S];
 	PLU_DEV void push(int sp, int32_t v) { if (S > 0 && sp < S) sm[sp * PLU_WALK_CTA] = v; else loc[sp - S] = v; }
 	PLU_DEV int32_t pop(int sp) const { return (S > 0 && sp < S) ? sm[sp * PLU_WALK_CTA] : loc[sp - S]; }
 };
@@ -300,6 +301,8 @@ struct fast_walker {
 	float best_t; int32_t best, best_rank, cur; int sp;
 	// the stack itself (walk_stack) is a separate object of the caller, so that these scalars stay in registers
 
+	template <bool COUNT>
+	PLU_DEV void begin_walk(const scene_ref& sc, const ray& r, trace_counts*) { begin(sc, r); }
 	PLU_DEV void begin(const scene_ref& sc, const ray& r) {
 		const float ix = 1.f / r.d.x, iy = 1.f / r.d.y, iz = 1.f / r.d.z;
 		ex2 = pk2(r.e.x, r.e.x); ey2 = pk2(r.e.y, r.e.y); ez2 = pk2(r.e.z, r.e.z);
@@ -331,49 +334,6 @@ struct fast_walker {
 		else if (h1) cur = d.y;
 		else { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; }
 	}
-	// both children of the pair (A, B) of a node against the ray: entry / exit distances
-	PLU_DEV void slab_pair(float lxa, float lxb, float lya, float lyb, float lza, float lzb, float hxa, float hxb, float hya, float hyb,
-	                       float hza, float hzb, float& na, float& fa, float& nb, float& fb) const {
-		float lx0, lx1, ly0, ly1, lz0, lz1, hx0, hx1, hy0, hy1, hz0, hz1;
-		upk2(submul2(pk2(lxa, lxb), ex2, ix2), lx0, lx1); upk2(submul2(pk2(lya, lyb), ey2, iy2), ly0, ly1);
-		upk2(submul2(pk2(lza, lzb), ez2, iz2), lz0, lz1); upk2(submul2(pk2(hxa, hxb), ex2, ix2), hx0, hx1);
-		upk2(submul2(pk2(hya, hyb), ey2, iy2), hy0, hy1); upk2(submul2(pk2(hza, hzb), ez2, iz2), hz0, hz1);
-		na = fmax3f(fminf(lx0, hx0), fminf(ly0, hy0), fminf(lz0, hz0)); fa = fmin3f(fmaxf(lx0, hx0), fmaxf(ly0, hy0), fmaxf(lz0, hz0));
-		nb = fmax3f(fminf(lx1, hx1), fminf(ly1, hy1), fminf(lz1, hz1)); fb = fmin3f(fmaxf(lx1, hx1), fmaxf(ly1, hy1), fmaxf(lz1, hz1));
-	}
-	// one wide node (cur >= 0): four slots in one pass, nearest first, the other hits on the stack farthest first.
-	// The boxes are the fast BVH's own (grandchild boxes), the tests and the culling rule are node_step's, so the
-	// set of leaves that can hold the closest hit is still always visited; only the visiting order differs.
-	template <bool COUNT, class STK>
-	PLU_DEV void node_step_wide(const wide_node* nodes, STK& stack, trace_counts* tc) {
-		const wide_node* nd = nodes + cur;
-		const float4 lx = __ldg(&nd->lox), ly = __ldg(&nd->loy), lz = __ldg(&nd->loz);
-		const float4 hx = __ldg(&nd->hix), hy = __ldg(&nd->hiy), hz = __ldg(&nd->hiz);
-		const int4 rf = __ldg(&nd->ref);
-		if (COUNT) tc->nodes++;
-		const float cull = best_t + fabsf(best_t) * 1e-5f;
-		float n0, f0, n1, f1, n2, f2, n3, f3;
-		slab_pair(lx.x, lx.y, ly.x, ly.y, lz.x, lz.y, hx.x, hx.y, hy.x, hy.y, hz.x, hz.y, n0, f0, n1, f1);
-		slab_pair(lx.z, lx.w, ly.z, ly.w, lz.z, lz.w, hx.z, hx.w, hy.z, hy.w, hz.z, hz.w, n2, f2, n3, f3);
-		const bool h0 = !(f0 < n0) && !(f0 < 0.f) && !(n0 > cull) && rf.x != PLU_WIDE_EMPTY;
-		const bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull) && rf.y != PLU_WIDE_EMPTY;
-		const bool h2 = !(f2 < n2) && !(f2 < 0.f) && !(n2 > cull) && rf.z != PLU_WIDE_EMPTY;
-		const bool h3 = !(f3 < n3) && !(f3 < 0.f) && !(n3 > cull) && rf.w != PLU_WIDE_EMPTY;
-		const int c = (int)h0 + (int)h1 + (int)h2 + (int)h3;
-		if (c == 0) { if (sp > 0) cur = stack.pop(--sp); else cur = DONE; return; }
-		// misses sort behind every hit
-		// (a NaN entry distance — zero or NaN direction — sorts first, so that no miss can slip in front of a hit)
-		float k0 = h0 ? (n0 == n0 ? n0 : -INFINITY) : INFINITY, k1 = h1 ? (n1 == n1 ? n1 : -INFINITY) : INFINITY;
-		float k2 = h2 ? (n2 == n2 ? n2 : -INFINITY) : INFINITY, k3 = h3 ? (n3 == n3 ? n3 : -INFINITY) : INFINITY;
-		int32_t r0 = rf.x, r1 = rf.y, r2 = rf.z, r3 = rf.w;
-#define PLU_CSWAP(ka, ra, kb, rb) { const bool s_ = kb < ka; const float tk_ = s_ ? kb : ka; const int32_t tr_ = s_ ? rb : ra; kb = s_ ? ka : kb; rb = s_ ? ra : rb; ka = tk_; ra = tr_; }
-		PLU_CSWAP(k0, r0, k1, r1) PLU_CSWAP(k2, r2, k3, r3) PLU_CSWAP(k0, r0, k2, r2) PLU_CSWAP(k1, r1, k3, r3) PLU_CSWAP(k1, r1, k2, r2)
-#undef PLU_CSWAP
-		if (c > 3) stack.push(sp++, r3);
-		if (c > 2) stack.push(sp++, r2);
-		if (c > 1) stack.push(sp++, r1);
-		cur = r0;
-	}
 	// one leaf: its <= 4 surface records
 	template <bool COUNT>
 	PLU_DEV void leaf_test(const float4* leaves, const ray& r, int32_t ref, trace_counts* tc) {
@@ -397,27 +357,24 @@ struct fast_walker {
 	// is_delta()): the first hit ends the walk.  Whether a hit exists does not depend on the visiting order, and
 	// distance culling only starts after a first hit, so the answer is the closest-hit walk's.
 	template <bool COUNT, class STK>
-	PLU_DEV void round(const fast_node* nodes, const wide_node* wide, const float4* leaves, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
-		if (PLU_WIDE_WALK && wide != nullptr) { while (cur >= 0) node_step_wide<COUNT>(wide, stack, tc); }
-		else { while (cur >= 0) node_step<COUNT>(nodes, stack, tc); }
+	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
+		const fast_node* nodes = sc.fast_nodes;
+		while (cur >= 0) node_step<COUNT>(nodes, stack, tc);
 		if (cur == DONE) return;
-		leaf_test<COUNT>(leaves, r, cur, tc);
+		leaf_test<COUNT>(sc.fast_leaf, r, cur, tc);
 		if (sp > 0 && !(any_hit && best >= 0)) cur = stack.pop(--sp); else cur = DONE;
 	}
 };
 
 template <bool COUNT, int S>
 PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
-	const fast_node* nodes = sc.fast_nodes;
-	const float4* leaves = sc.fast_leaf;   // 3 x float4 per leaf slot, in leaf order (plugpu.cu: upload)
 	fast_walker w; w.begin(sc, r);
 	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
 	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
 	// "while-while" walk: every lane first descends to its next leaf, then the warp tests leaves together;
 	// with one if/else per step (r01f: 8.6 of 32 threads active per instruction) node and leaf work of
 	// different lanes alternated serially
-	const wide_node* wide = sc.wide_nodes;
-	while (w.cur != fast_walker::DONE) w.round<COUNT>(nodes, wide, leaves, r, stack, tc, any_hit);
+	while (w.cur != fast_walker::DONE) w.round<COUNT>(sc, r, stack, tc, any_hit);
 	t_out = w.best_t; prim_out = w.best;
 	return w.best >= 0;
 }
@@ -497,18 +454,18 @@ struct general_walker {
 	}
 };
 
-template <bool COUNT, int S>
-PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
-	const walk_node* nodes = sc.walk_nodes;
-	general_walker w;
-	w.begin(r, sc.sphere_rmin, sc.has_spheres ? sc.sphere_rmax : -1.f);
-	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
-	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
-	int sp = 0;
+// The walk as a resumable state machine (like fast_walker): k_extend_pt keeps one per lane across refills — the cost of
+// these rays is heavy-tailed (a cone ray whose near candidates the reference's own boxes reject looks at thousands of
+// surfaces, the median ray at a dozen), so one ray per lane per iteration would idle most of a warp.
+struct pruned_walker : general_walker {
+	static constexpr int32_t DONE = (int32_t)0x80000000;
+	int32_t cur; int sp;
+
 	// one child of an interior node: a leaf is tested at once (the reference tests leaves without a box, bvh_tree.cpp:40),
 	// an interior child yields its key (+inf: the reference does not enter it, or nothing in it can improve the result)
-	auto visit = [&](int32_t node, int32_t k, float cull) -> float {
-		const walk_node* nd = nodes + node;
+	template <bool COUNT>
+	PLU_DEV float visit(const scene_ref& sc, const ray& r, int32_t node, int32_t k, float cull, trace_counts* tc) {
+		const walk_node* nd = sc.walk_nodes + node;
 		const float4 a = __ldg(&nd->a), b = __ldg(&nd->b);
 		if (k == 1) {
 			const int32_t tag = __float_as_int(a.w), prim = __float_as_int(b.w);
@@ -516,34 +473,41 @@ PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, i
 			if (COUNT) tc->prims++;
 			if (tag == PLU_PRIM_BOX) h = box_t(a, b, r, PLU_T_MAX, t);
 			else if (tag == PLU_PRIM_SPHERE) h = sphere_t(make_float4(a.x, a.y, a.z, b.x), r, PLU_T_MAX, t);
-			else { const float4* p = sc.prim(prim); h = triangle_t(__ldg(p), __ldg(p + 1), __ldg(p + 2), r, PLU_T_MAX, t); }
+			else { const float4* p = sc.prim(prim); h = triangle_t(p[0], p[1], p[2], r, PLU_T_MAX, t); }   // (the blob may be staged in shared memory: no __ldg)
 			if (h) {
 				const int32_t rank = __float_as_int(__ldg(&nd->d).w);
-				if (w.best < 0 || t < w.best_t || (t == w.best_t && rank > w.best_rank)) { w.best_t = t; w.best = prim; w.best_rank = rank; }
+				if (best < 0 || t < best_t || (t == best_t && rank > best_rank)) { best_t = t; best = prim; best_rank = rank; }
 			}
 			return INFINITY;
 		}
-		float tmin, tmax; slabs_rrd(mk3(a), mk3(b), r.e, w.rrd, tmin, tmax);   // the reference's own test on its own box
+		float tmin, tmax; slabs_rrd(mk3(a), mk3(b), r.e, rrd, tmin, tmax);   // the reference's own test on its own box
 		if (!(tmax >= tmin)) return INFINITY;
-		const float4 c = __ldg(&nd->c), d = __ldg(&nd->d);
-		return w.child_key(c.x, c.y, c.z, d.x, d.y, d.z, d.w, cull);
-	};
-	int32_t cur = 0;
-	if (sc.n_prims == 1) { visit(0, 1, 3.0e38f); cur = -1; }
-	else {   // the root is tested like any interior node
-		float tmin, tmax; const walk_node* nd = nodes;
-		slabs_rrd(mk3(__ldg(&nd->a)), mk3(__ldg(&nd->b)), r.e, w.rrd, tmin, tmax);
-		if (!(tmax >= tmin)) cur = -1;
+		const float4 c = __ldg(&nd->c), d4 = __ldg(&nd->d);
+		return child_key(c.x, c.y, c.z, d4.x, d4.y, d4.z, d4.w, cull);
 	}
-	while (cur >= 0) {
-		const int32_t k = __float_as_int(__ldg(&nodes[cur].c).w);
+	template <bool COUNT>
+	PLU_DEV void begin_walk(const scene_ref& sc, const ray& r, trace_counts* tc) {
+		begin(r, sc.sphere_rmin, sc.has_spheres ? sc.sphere_rmax : -1.f);
+		sp = 0; cur = 0;
+		if (sc.n_prims == 1) { visit<COUNT>(sc, r, 0, 1, 3.0e38f, tc); cur = DONE; }
+		else {   // the root is tested like any interior node
+			float tmin, tmax; const walk_node* nd = sc.walk_nodes;
+			slabs_rrd(mk3(__ldg(&nd->a)), mk3(__ldg(&nd->b)), r.e, rrd, tmin, tmax);
+			if (!(tmax >= tmin)) cur = DONE;
+		}
+	}
+	// one round: expand the interior node `cur` (both children: leaves are tested, interior ones ranked), move on
+	template <bool COUNT, class STK>
+	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
+		if (cur == DONE) return;
+		const int32_t k = __float_as_int(__ldg(&sc.walk_nodes[cur].c).w);
 		const int32_t kl = k >> 1, L = cur + 1, R = cur + 2 * kl;
 		if (COUNT) tc->nodes++;
-		float cull = w.best >= 0 ? w.best_t + fabsf(w.best_t) * 1e-5f : 3.0e38f;
-		const float k0 = visit(L, kl, cull);
-		if (w.best >= 0) cull = w.best_t + fabsf(w.best_t) * 1e-5f;
-		const float k1 = visit(R, k - kl, cull);
-		if (any_hit && w.best >= 0) break;
+		float cull = best >= 0 ? best_t + fabsf(best_t) * 1e-5f : 3.0e38f;
+		const float k0 = visit<COUNT>(sc, r, L, kl, cull, tc);
+		if (best >= 0) cull = best_t + fabsf(best_t) * 1e-5f;
+		const float k1 = visit<COUNT>(sc, r, R, k - kl, cull, tc);
+		if (any_hit && best >= 0) { cur = DONE; return; }
 		const bool h0 = k0 < INFINITY, h1 = k1 < INFINITY;
 		if (h0 && h1) {
 			const bool first1 = k1 < k0;
@@ -552,11 +516,20 @@ PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, i
 		} else if (h0) cur = L;
 		else if (h1) cur = R;
 		else {
-			// a stacked subtree may have fallen behind the best hit found since it was pushed: its key is re-derived on
-			// expansion (visit() of its children), so popping it unconditionally only costs those two visits
-			if (sp > 0) cur = stack.pop(--sp); else cur = -1;
+			// a stacked subtree may have fallen behind the best hit found since it was pushed: its children are ranked
+			// again when it is expanded, so popping it unconditionally costs those two visits at most
+			if (sp > 0) cur = stack.pop(--sp); else cur = DONE;
 		}
 	}
+};
+
+template <bool COUNT, int S>
+PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
+	pruned_walker w;
+	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
+	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
+	w.begin_walk<COUNT>(sc, r, tc);
+	while (w.cur != pruned_walker::DONE) w.round<COUNT>(sc, r, stack, tc, any_hit);
 	t_out = w.best_t; prim_out = w.best;
 	return w.best >= 0;
 }

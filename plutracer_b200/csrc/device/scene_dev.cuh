@@ -29,14 +29,6 @@ struct ref_node { float4 lo, hi; };
 //   triangle a = (v0 | surface id)       b = (v1 | kind<<30 | tie rank)       c = (v2 | -)
 struct fast_node { float4 a, b, c; int4 d; };
 
-// Four-child node collapsed from the fast BVH at upload (plugpu.cu: k_collapse_wide; opt-in, PLU_WIDE=1): wide
-// node i holds the GRANDCHILDREN of fast node i (slots 0,1 under child 0, slots 2,3 under child 1; a leaf child
-// keeps its own box in its first slot), so one step descends two levels with one dependent load instead of two.
-// Same index space as fast_node (only nodes reached through grandchild links are ever read), 128 B = one line.
-//   lox..hiz = the plane of the four slots; ref = child refs as in fast_node::d, PLU_WIDE_EMPTY for an unused slot.
-struct wide_node { float4 lox, loy, loz, hix, hiy, hiz; int4 ref; int4 pad; };
-#define PLU_WIDE_EMPTY ((int32_t)0x80000000)
-
 // Node of the pruned reference-tree walk (scenes with spheres, isect.cuh: trace_ref_pruned), 64 B, same pre-order index
 // space as ref_node:
 //   interior  a = ref lo | skip     b = ref hi | -1      c = tight min | leaf count k (int)   d = tight max | half diagonal
@@ -58,7 +50,6 @@ struct scene_ref {
 	const fast_node* fast_nodes;    // null: traverse the reference tree
 	const int32_t* fast_prim_index; // leaf slots -> prim ids
 	const float4* fast_leaf;        // leaf slots -> surface records (see fast_node)
-	const wide_node* wide_nodes;    // null: walk fast_nodes two children at a time
 	const walk_node* walk_nodes;    // non-null: scenes with spheres walk the reference tree with tight-box pruning
 	int32_t n_fast_nodes;
 	int32_t has_spheres;

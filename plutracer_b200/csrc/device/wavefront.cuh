@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 #define PT_REFILL 12u
 #endif
 
-template <bool COUNT>
+template <bool COUNT, class WALKER = fast_walker>
 __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	const int bounce = wave_vertex(wb, bounce_arg);
@@ -381,10 +381,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
 	const float nl = (float)sc.n_lights;
-	const fast_node* nodes = sc.fast_nodes;
-	const wide_node* wide = sc.wide_nodes;
-	const float4* leaves = sc.fast_leaf;
-	fast_walker w; w.cur = fast_walker::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
+	WALKER w; w.cur = WALKER::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
 	__shared__ int32_t s_stack[PLU_SSTK > 0 ? PLU_SSTK : 1][PLU_SSTK > 0 ? PLU_CTA : 1];
 	walk_stack<PLU_SSTK> stack; stack.sm = &s_stack[0][PLU_SSTK > 0 ? threadIdx.x : 0];
 	bool have = false, exhausted = false;
@@ -394,7 +391,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 	for (;;) {
 		// retire the lanes whose walk has ended
 		int cls = 0;
-		if (have && w.cur == fast_walker::DONE) {
+		if (have && w.cur == WALKER::DONE) {
 			cls = extend_finish(sc, recs, wb.rad, bounce, slot, r, flags, w.best >= 0, w.best_t, w.best, nl);
 			have = false;
 		}
@@ -422,7 +419,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 				slot = ident ? idx : q[idx];
 				float4 o = recs[4 * (size_t)slot], d = recs[4 * (size_t)slot + 1];
 				r.e = mk3(o); r.d = mk3(d); flags = __float_as_int(d.w);
-				w.begin(sc, r);
+				w.template begin_walk<COUNT>(sc, r, &tc);
 				have = true;
 			}
 			c_next = min(c_next + (uint32_t)__popc(idle), c_end);
@@ -431,8 +428,8 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ s
 		// walk until fewer than min_active lanes are still walking (to the end once the queue is exhausted)
 		const uint32_t min_active = exhausted ? 1u : 33u - refill;
 		for (;;) {
-			w.round<COUNT>(nodes, wide, leaves, r, stack, &tc);
-			if ((uint32_t)__popc(__ballot_sync(FULL, w.cur != fast_walker::DONE)) < min_active) break;
+			w.template round<COUNT>(sc, r, stack, &tc);
+			if ((uint32_t)__popc(__ballot_sync(FULL, w.cur != WALKER::DONE)) < min_active) break;
 		}
 	}
 	if (COUNT) {

@@ -40,7 +40,6 @@ struct plu_gpu_ctx {
 	unsigned char* d_blob = nullptr;
 	float *d_tri_uv = nullptr, *d_tri_normal = nullptr, *d_texels = nullptr;
 	fast_node* d_fast = nullptr; int32_t* d_fast_index = nullptr; float4* d_fast_leaf = nullptr;
-	wide_node* d_wide = nullptr;   // PLU_WIDE=1: four-child nodes collapsed from d_fast (k_collapse_wide)
 	walk_node* d_walk = nullptr;   // scenes with spheres on the fast path: the reference tree with tight boxes (trace_ref_pruned)
 	bool blob_in_smem = false;
 	bool use_fast = false;
@@ -195,7 +194,6 @@ extern "C" int plu_gpu_device_count(const plu_gpu_ctx* ctx) { return ctx ? 1 + (
 
 static void free_scene(plu_gpu_ctx* ctx) {
 	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
-	cudaFree(ctx->d_wide); ctx->d_wide = nullptr;
 	cudaFree(ctx->d_walk); ctx->d_walk = nullptr;
 	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index); cudaFree(ctx->d_fast_leaf); ctx->d_fast_leaf = nullptr;
 	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
@@ -243,43 +241,6 @@ static double wall_ms() { return std::chrono::duration<double, std::milli>(std::
 
 extern "C" int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* d) { return plu_gpu_upload_scene_ex(ctx, d, PLU_BUILD_DEVICE, nullptr); }
 
-// Four-child nodes from the two-child fast BVH (scene_dev.cuh: wide_node): node i <- the children of its children.
-__device__ inline void wide_take(const fast_node& B, int j, float* lo, float* hi) {
-	const float* a = &B.a.x; const float* b = &B.b.x; const float* c = &B.c.x;
-	lo[0] = a[j]; lo[1] = a[2 + j]; lo[2] = b[j]; hi[0] = b[2 + j]; hi[1] = c[j]; hi[2] = c[2 + j];
-}
-__global__ void k_collapse_wide(int32_t n, const fast_node* in, wide_node* out) {
-	const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n) return;
-	const fast_node B = in[i];
-	float lo[4][3], hi[4][3]; int32_t ref[4];
-	for (int s = 0; s < 4; ++s) { ref[s] = PLU_WIDE_EMPTY; for (int k = 0; k < 3; ++k) { lo[s][k] = INFINITY; hi[s][k] = -INFINITY; } }
-	for (int j = 0; j < 2; ++j) {
-		const int32_t c = j ? B.d.y : B.d.x;
-		if (c >= 0) {
-			const fast_node C = in[c];
-			for (int k = 0; k < 2; ++k) {
-				const int32_t r = k ? C.d.y : C.d.x;
-				wide_take(C, k, lo[2 * j + k], hi[2 * j + k]);
-				ref[2 * j + k] = (r < 0 && ((~r) & 7) == 0) ? PLU_WIDE_EMPTY : r;   // a leaf without surfaces (k_root_leaf) is no child
-			}
-		} else {
-			wide_take(B, j, lo[2 * j], hi[2 * j]);
-			ref[2 * j] = ((~c) & 7) == 0 ? PLU_WIDE_EMPTY : c;
-		}
-	}
-	wide_node W;
-	W.lox = make_float4(lo[0][0], lo[1][0], lo[2][0], lo[3][0]); W.loy = make_float4(lo[0][1], lo[1][1], lo[2][1], lo[3][1]);
-	W.loz = make_float4(lo[0][2], lo[1][2], lo[2][2], lo[3][2]); W.hix = make_float4(hi[0][0], hi[1][0], hi[2][0], hi[3][0]);
-	W.hiy = make_float4(hi[0][1], hi[1][1], hi[2][1], hi[3][1]); W.hiz = make_float4(hi[0][2], hi[1][2], hi[2][2], hi[3][2]);
-	W.ref = make_int4(ref[0], ref[1], ref[2], ref[3]); W.pad = make_int4(0, 0, 0, 0);
-	out[i] = W;
-}
-
-static int upload_single(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats);
-
-// A multi-device context deep-copies the scene to every device and builds the traversal structures on each (one host
-// thread per device; the builds are deterministic, so all devices hold byte-identical tables).
 // ---- walk_node table of trace_ref_pruned (scene_dev.cuh): the reference tree + the tight box of every subtree ----
 // float <-> unsigned images that keep the order, so that boxes merge with atomicMin / atomicMax
 __device__ __forceinline__ uint32_t f2ord(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
@@ -333,6 +294,10 @@ __global__ void k_walk_finish(int32_t n_nodes, walk_node* out) {
 	out[i].c = c; out[i].d = d;
 }
 
+static int upload_single(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats);
+
+// A multi-device context deep-copies the scene to every device and builds the traversal structures on each (one host
+// thread per device; the builds are deterministic, so all devices hold byte-identical tables).
 extern "C" int plu_gpu_upload_scene_ex(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_t build, plu_build_stats* stats) {
 	if (!ctx) return PLU_E_ARG;
 	if (ctx->peers.empty()) return upload_single(ctx, d, build, stats);
@@ -469,19 +434,15 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 	}
 	bs.ms_total = t_build;
 	if (stats) *stats = bs;
+	{   // the traversal stacks hold PLU_WALK_DEPTH_MAX entries (isect.cuh: walk_stack): refuse a tree that could overflow them
+		int lg = 0; while (((size_t)1 << lg) < std::max<size_t>(n, 2)) ++lg;
+		if (41 + lg > PLU_WALK_DEPTH_MAX || bs.levels_fast > PLU_WALK_DEPTH_MAX) { free_scene(ctx); return fail(ctx, PLU_E_ARG, "fast BVH deeper than the traversal stack"); }
+	}
 	sc.fast_nodes = use_fast ? ctx->d_fast : nullptr;
 	ctx->use_fast = use_fast;
 	ctx->has_specular = false;
 	for (int32_t i = 0; i < d->n_materials; ++i) if (d->materials[i].tag >= PLU_MAT_PERFECT_REFLECTION && d->materials[i].tag <= PLU_MAT_GLASS) ctx->has_specular = true;
 	sc.fast_prim_index = ctx->d_fast_index; sc.fast_leaf = ctx->d_fast_leaf;
-	sc.wide_nodes = nullptr;
-	if (PLU_WIDE_WALK && ctx->d_fast != nullptr && sc.n_fast_nodes > 0 && std::getenv("PLU_WIDE") != nullptr && std::atoi(std::getenv("PLU_WIDE")) > 0) {
-		CU(cudaMalloc(&ctx->d_wide, (size_t)sc.n_fast_nodes * sizeof(wide_node)));
-		k_collapse_wide<<<(sc.n_fast_nodes + 255) / 256, 256, 0, ctx->stream>>>(sc.n_fast_nodes, ctx->d_fast, ctx->d_wide);
-		CU(cudaGetLastError());
-		CU(cudaStreamSynchronize(ctx->stream));
-		sc.wide_nodes = ctx->d_wide;
-	}
 	sc.walk_nodes = nullptr;
 	if (sc.has_spheres && sc.n_ref_nodes > 0) {   // (small scenes only reach it with PLU_RENDER_BVH_FAST)
 		// sphere::hit is fed non-unit directions, which no walk of the SAH tree can follow: those scenes walk the reference
@@ -574,14 +535,15 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 // dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
 struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_prim, g_ext_pt, g_shade[2], g_conn, g_acc; };
 
-// Waves on the fast BVH of a sphere-free scene extend with persistent warps (k_extend_pt) and start with k_generate; all
-// other waves start with k_primary (camera ray generation fused into the first extension).
-static bool wave_uses_pt(const scene_ref& sc, const launch_cfg& c) { return !c.smem && sc.fast_nodes != nullptr && !sc.has_spheres && !c.no_pt; }
+// Waves of a large scene (fast BVH / pruned reference tree) extend with persistent warps (k_extend_pt) and start with
+// k_generate; all other waves start with k_primary (camera ray generation fused into the first extension).
+static bool wave_uses_pt(const scene_ref& sc, const launch_cfg& c) { return !c.smem && sc.fast_nodes != nullptr && !c.no_pt; }
 
 static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
 	launch_cfg c; std::memset(&c, 0, sizeof(c));   // (the struct is part of the graph key: no indeterminate padding)
 	c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
-	c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
+	if (ctx->sc.has_spheres) c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true, pruned_walker>, 0) : grid_for(ctx, k_extend_pt<false, pruned_walker>, 0);
+	else c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
 	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
 	c.g_gen = grid_for(ctx, k_generate, 0);
@@ -624,14 +586,24 @@ struct wave_profiler {
 // The wave's descriptor must already be on its way to wb.desc on `st` (put_desc); nothing below depends on the wave, so
 // the same sequence serves every wave of a render (and is what wave_graph_for records).  `b` is the path vertex, or
 // PLU_B_LOOP / PLU_B_LOOP_NEXT inside the graph's while loop (the kernels then read the vertex from device memory).
+// persistent warps with lane refill over the scene's walk: the SAH tree, or (scenes with spheres) the pruned reference tree
+static void launch_extend_pt(plu_gpu_ctx* ctx, const scene_ref& sc, const launch_cfg& c, cudaStream_t st, const wave_buffers& wb, int b) {
+	if (sc.has_spheres) {
+		if (c.count) k_extend_pt<true, pruned_walker><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+		else k_extend_pt<false, pruned_walker><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+	} else {
+		if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+		else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+	}
+}
+
 static void launch_head(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices, const launch_cfg& c, cudaStream_t st, wave_profiler* pf, int P, bool pt) {
 	wave_buffers& wb = ctx->wbs[P];
 	cudaMemsetAsync(wb.counters, 0, (size_t)(max_vertices + 2) * CNT_STRIDE * sizeof(uint32_t), st);   // incl. the loop word, row max_vertices + 1
 	pf->mark(-1, st);
 	if (pt) {
 		k_generate<<<c.g_gen, 256, 0, st>>>(sc, wb); pf->mark(0, st);
-		if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, 0, ctx->pt_refill);
-		else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, 0, ctx->pt_refill);
+		launch_extend_pt(ctx, sc, c, st, wb, 0);
 	} else if (c.smem) {   // k_primary: generate + extend of vertex 0 in one kernel (its time is booked under "extend")
 		if (c.count) k_extend<true, true, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0); else k_extend<true, false, true><<<c.g_prim, PLU_CTA, c.sm_ext, st>>>(sc, wb, 0);
 	} else {
@@ -643,8 +615,7 @@ static void launch_head(plu_gpu_ctx* ctx, const scene_ref& sc, int max_vertices,
 static void launch_extend(plu_gpu_ctx* ctx, const scene_ref& sc, const launch_cfg& c, cudaStream_t st, wave_profiler* pf, int P, bool pt, int b) {
 	wave_buffers& wb = ctx->wbs[P];
 	if (pt) {   // fast BVH, no sphere (whose non-unit-direction rays need another walk): persistent warps with lane refill
-		if (c.count) k_extend_pt<true><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
-		else k_extend_pt<false><<<c.g_ext_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill);
+		launch_extend_pt(ctx, sc, c, st, wb, b);
 	} else if (c.smem) {
 		if (c.count) k_extend<true, true><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);
 		else k_extend<true, false><<<c.g_ext, PLU_CTA, c.sm_ext, st>>>(sc, wb, b);

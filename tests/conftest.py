@@ -62,5 +62,5 @@ def pytest_sessionfinish(session, exitstatus):
 
 
 REF_SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's scenes (BASELINE.json configs)
-OWN_SCENES = ["atrium", "colonnade", "shard", "gallery"]                         # scenes/ of this repo
+OWN_SCENES = ["atrium", "colonnade", "shard", "gallery", "trilight"]                         # scenes/ of this repo
 SCENES = REF_SCENES + OWN_SCENES

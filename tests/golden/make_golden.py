@@ -30,7 +30,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "plu_ref")
 REF_SCENES = os.environ.get("PLU_REFERENCE", "/root/reference") + "/scenes"
 SCENES = ["minimal0", "cornell-box", "glass0", "refrac0", "room"]   # the reference's own scenes/ (BASELINE.json configs)
-OWN_SCENES = ["atrium", "colonnade", "shard", "gallery"]   # this repo's scenes/: all material kinds, scripted objects + lens, triangle mesh
+OWN_SCENES = ["atrium", "colonnade", "shard", "gallery", "trilight"]   # this repo's scenes/: all material kinds, scripted objects + lens, triangle mesh
 PW, PH = 96, 72
 SW, SH, SN, SSEED = 32, 24, 2, 7
 
