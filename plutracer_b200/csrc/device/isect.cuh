@@ -534,11 +534,19 @@ PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, i
 	return w.best >= 0;
 }
 
-template <bool COUNT, bool SMEM>
+// scene->hit.  Kernels of scenes staged in shared memory (SMEM: every named scene) only ever walk the reference's own
+// small tree; the large-scene walks live in the global-memory kernels alone (PLU_RENDER_BVH_FAST runs a small scene
+// through those kernels, which is how the tests exercise them on the reference's scenes) — keeping them out of the staged
+// kernels keeps those at 64 registers without spills.
+// WALKS: which large-scene walks the caller compiles in (a hot kernel is instantiated per walk so that it carries one).
+#define PLU_WALKS_BOTH 0
+#define PLU_WALKS_FAST 1     // sphere-free scene: the SAH tree
+#define PLU_WALKS_PRUNED 2   // scene with spheres: the pruned reference tree
+template <bool COUNT, bool SMEM, int WALKS = PLU_WALKS_BOTH>
 PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc, bool any_hit = false) {
-	if (sc.fast_nodes != nullptr) {
-		if (sc.has_spheres) return trace_ref_pruned<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
-		return trace_fast<COUNT, SMEM ? 0 : PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+	if (!SMEM && sc.fast_nodes != nullptr) {
+		if (WALKS == PLU_WALKS_PRUNED || (WALKS == PLU_WALKS_BOTH && sc.has_spheres)) return trace_ref_pruned<COUNT, PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+		return trace_fast<COUNT, PLU_SSTK>(sc, r, t, prim, tc, any_hit);
 	}
 	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT, SMEM>(sc, r, root_bound, t, prim, tc);
 	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);

@@ -241,7 +241,7 @@ PLU_DEV int primary_finish(const scene_ref& sc, float4* recs, float4* rad, uint3
 // into shared memory by cp.async during iteration i-1, issues the gathers of iteration i+1 and loads
 // the queue entry of iteration i+2; queue pushes started in iteration i are completed in iteration i+1.
 template <bool SMEM, bool COUNT, bool PRIMARY = false>
-__global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+__global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
 	const int bounce = PRIMARY ? 0 : wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
@@ -354,6 +354,8 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 }
 
 // ---- k_extend_pt ----------------------------------------------------------------------------------------------
+// (__launch_bounds__(.., 4) on the traversal kernels: 64 registers = 32 warps per SM; the walks are latency-bound and at 68
+// registers / 24 warps the 1M-box scene ran 7 % slower, profiles/r02_summary.md)
 // k_extend for scenes that walk the fast BVH: persistent warps that REFILL finished lanes.  With one ray per lane
 // per iteration a warp runs as long as its longest ray (profiles/r01_summary.md: 10-13 of 32 threads active per
 // instruction on the 1M-surface scene, coherent camera rays included); here a lane whose walk ends waits only
@@ -368,7 +370,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_extend(const __grid_constant__ scen
 #endif
 
 template <bool COUNT, class WALKER = fast_walker>
-__global__ void __launch_bounds__(PLU_CTA) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
+__global__ void __launch_bounds__(PLU_CTA, 4) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	const int bounce = wave_vertex(wb, bounce_arg);
 	float4* const recs = wb.rec;
@@ -652,8 +654,8 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 // ---- k_connect ------------------------------------------------------------------------------------------------
 // The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
 // `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
-template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+template <bool SMEM, bool COUNT, int WALKS = PLU_WALKS_BOTH>
+__global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
 	const int bounce = wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	float4* const recs = wb.rec;
@@ -700,7 +702,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 #else
 				const bool any_hit = false;
 #endif
-				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc, any_hit);
+				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc, any_hit);
 				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
 				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
 			}
@@ -708,7 +710,7 @@ __global__ void __launch_bounds__(PLU_CTA) k_connect(const __grid_constant__ sce
 				r.d = mk3(row[3 * PLU_CTA]);
 				float t; int32_t prim;
 				rays++;
-				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
+				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc);
 				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(row[4 * PLU_CTA]); any = true; }
 			}
 			f3 T = mk3(T4);

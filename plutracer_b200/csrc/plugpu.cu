@@ -539,9 +539,11 @@ struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, s
 // k_generate; all other waves start with k_primary (camera ray generation fused into the first extension).
 static bool wave_uses_pt(const scene_ref& sc, const launch_cfg& c) { return !c.smem && sc.fast_nodes != nullptr && !c.no_pt; }
 
-static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count) {
+// force_global: PLU_RENDER_BVH_FAST on a scene that would be staged in shared memory — it then runs through the
+// global-memory kernels (the only ones that hold the large-scene walks)
+static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count, bool force_global = false) {
 	launch_cfg c; std::memset(&c, 0, sizeof(c));   // (the struct is part of the graph key: no indeterminate padding)
-	c.smem = ctx->blob_in_smem; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
+	c.smem = ctx->blob_in_smem && !force_global; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
 	if (ctx->sc.has_spheres) c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true, pruned_walker>, 0) : grid_for(ctx, k_extend_pt<false, pruned_walker>, 0);
 	else c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
@@ -646,7 +648,9 @@ static int launch_shade_connect(plu_gpu_ctx* ctx, const scene_ref& sc, const lau
 	}
 	pf->mark(2, st);
 	if (c.smem) { if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
-	else { if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	else if (sc.fast_nodes == nullptr) { if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	else if (sc.has_spheres) { if (c.count) k_connect<false, true, PLU_WALKS_PRUNED><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false, PLU_WALKS_PRUNED><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	else { if (c.count) k_connect<false, true, PLU_WALKS_FAST><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false, PLU_WALKS_FAST><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
 	pf->mark(3, st);
 	return launches;
 }
@@ -800,7 +804,7 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 	uint32_t want_max = adaptive ? (uint32_t)std::max<int64_t>(want, std::min<int64_t>((int64_t)PLU_WAVE_PATHS_MAX, wh * (int64_t)count / 4)) : want;
 	rc = ensure_wave(ctx, want_max);
 	if (rc != PLU_OK) return rc;
-	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0);
+	launch_cfg cfg = make_cfg(ctx, (p->flags & PLU_RENDER_COUNT_BVH) != 0, sc.fast_nodes != nullptr);
 	cfg.no_pt = (p->flags & PLU_RENDER_NO_LANE_REFILL) != 0;
 	w.use_dirty = wave_uses_pt(sc, cfg) ? 0 : 1;
 	wave_profiler prof; prof.on = (p->flags & PLU_RENDER_PROFILE) != 0;
@@ -1017,10 +1021,11 @@ static int trace_common(plu_gpu_ctx* ctx, int64_t n, const float* o3, const floa
 	}
 	CUX(cudaMalloc(&d_id, (size_t)n * 4)); CUX(cudaMalloc(&d_t, (size_t)n * 4)); CUX(cudaMalloc(&d_n, (size_t)n * 12));
 	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+	const bool staged = ctx->blob_in_smem && sc.fast_nodes == nullptr;   // the large-scene walks live in the global-memory kernels
 	if (flags & PLU_RENDER_COUNT_BVH) {
-		if (ctx->blob_in_smem) k_trace_rays<true, true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+		if (staged) k_trace_rays<true, true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
 		else k_trace_rays<false, true><<<grid, 256, 0, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
-	} else if (ctx->blob_in_smem) k_trace_rays<true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
+	} else if (staged) k_trace_rays<true><<<grid, 256, sc.blob_bytes, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
 	else k_trace_rays<false><<<grid, 256, 0, ctx->stream>>>(sc, n, d_o, d_d, pw, ph, d_id, d_t, d_n);
 	CUX(cudaGetLastError());
 	CUX(cudaMemcpyAsync(surf_id, d_id, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1058,7 +1063,7 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 	const int32_t count = p->sample_count > 0 ? p->sample_count : p->n_strata * p->n_strata;
 	rc = ensure_wave(ctx, (uint32_t)std::min<int64_t>((int64_t)1 << 22, std::max<int64_t>(pixel_count, 1) * count));
 	if (rc != PLU_OK) return rc;
-	launch_cfg cfg = make_cfg(ctx, false);
+	launch_cfg cfg = make_cfg(ctx, false, sc.fast_nodes != nullptr);
 	w.use_dirty = wave_uses_pt(sc, cfg) ? 0 : 1;
 	std::vector<float4> host; std::vector<uint32_t> dirty;
 	for (int64_t p0 = pixel_begin; p0 < pixel_begin + pixel_count;) {
