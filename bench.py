@@ -57,6 +57,19 @@ CONFIGS = {
 }
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """One JSON line on the process's ORIGINAL stdout.  Everything else that writes to fd 1 (NCCL's version banner, a
+    library's printf) is sent to stderr for the whole run (main() re-points fd 1), so stdout carries the JSON lines only."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def config_names(arg):
     names = list(CONFIGS) if arg == "all" else [x for x in arg.split(",") if x]
     for x in names:
@@ -467,7 +480,7 @@ def bench_config(name, args, rank, world, local, host_group):
             line["e2e_torchrun"] = e2e_torchrun
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     if ctx is not None:
         ctx.close()
     del fb, flush
@@ -488,6 +501,11 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)
+
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist

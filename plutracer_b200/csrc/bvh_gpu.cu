@@ -171,10 +171,15 @@ inline int blocks(size_t n, int t = 256) { return (int)((n + (size_t)t - 1) / (s
 
 struct kv { float k; int32_t v; };
 
+// Scratch of the build: stream-ordered allocations (cudaMallocAsync on the build's stream).  cudaMalloc / cudaFree are
+// device-wide synchronisation points and, in a process that drives several GPUs with peer access enabled (the
+// multi-device context: NCCL), each one has to be mapped on every peer — dozens of them per build cost more than the
+// build itself.  The pool keeps the memory across builds (plugpu.cu sets the release threshold).
 struct dev_mem {   // frees everything it handed out
-	std::vector<void*> p;
-	template <class T> T* get(size_t count) { void* q = nullptr; if (cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)) != cudaSuccess) return nullptr; p.push_back(q); return (T*)q; }
-	~dev_mem() { for (void* q : p) cudaFree(q); }
+	std::vector<void*> p; cudaStream_t st;
+	explicit dev_mem(cudaStream_t s) : st(s) {}
+	template <class T> T* get(size_t count) { void* q = nullptr; if (cudaMallocAsync(&q, std::max<size_t>(count, 1) * sizeof(T), st) != cudaSuccess) return nullptr; p.push_back(q); return (T*)q; }
+	~dev_mem() { for (void* q : p) cudaFreeAsync(q, st); }
 };
 
 // host comparator of bvh_tree.cpp:23-27 for the tie fix-up
@@ -197,7 +202,7 @@ double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::
 // Part 1: the leaf order of the reference tree, into meta[].w (tie rank) and `order` (rank -> surface)
 bool ref_order_on_device(const plu_scene_desc* d, device_tables& t, int32_t* d_order, cudaStream_t st, plu_build_stats* stats, std::string& err) {
 	const int32_t n = d->n_prims;
-	dev_mem mem;
+	dev_mem mem(st);
 	float* cen = mem.get<float>(3 * (size_t)n);
 	unsigned long long* keys = mem.get<unsigned long long>(n); unsigned long long* keys2 = mem.get<unsigned long long>(n);
 	int32_t* order2 = mem.get<int32_t>(n);
@@ -615,7 +620,7 @@ __global__ void k_fast_leaf(int32_t n, const int32_t* idx, const float* prim, co
 
 // Part 3: the fast BVH
 bool fast_bvh_on_device(int32_t n, device_tables& t, cudaStream_t st, plu_build_stats* stats, std::string& err) {
-	dev_mem mem;
+	dev_mem mem(st);
 	float4* pa = mem.get<float4>(n); float4* pb = mem.get<float4>(n); float* cz = mem.get<float>(n);
 	int32_t* seg_of = mem.get<int32_t>(n); int32_t* idx_tmp = mem.get<int32_t>(n); int32_t* seg_tmp = mem.get<int32_t>(n);
 	int32_t* flag = mem.get<int32_t>(n); int32_t* pre = mem.get<int32_t>(n);
@@ -627,7 +632,7 @@ bool fast_bvh_on_device(int32_t n, device_tables& t, cudaStream_t st, plu_build_
 	bnode* nodes = mem.get<bnode>((size_t)n + 1); unsigned long long* node_key = mem.get<unsigned long long>((size_t)n + 1);
 	uint32_t* totals = mem.get<uint32_t>(2); float* root_box = mem.get<float>(6);
 	int32_t* idx = nullptr;
-	if (cudaMalloc(&idx, (size_t)n * sizeof(int32_t)) != cudaSuccess) { err = "cudaMalloc (fast index)"; return false; }
+	if (cudaMallocAsync(&idx, (size_t)n * sizeof(int32_t), st) != cudaSuccess) { err = "cudaMalloc (fast index)"; return false; }
 	t.d_fast_index = idx;
 	if (!pa || !pb || !cz || !seg_of || !idx_tmp || !seg_tmp || !flag || !pre || !segs || !next || !packed || !ranks || !seg_box || !bins || !splits || !nodes || !node_key || !totals || !root_box) {
 		err = "cudaMalloc (fast BVH scratch)"; return false;
@@ -674,7 +679,7 @@ bool fast_bvh_on_device(int32_t n, device_tables& t, cudaStream_t st, plu_build_
 	}
 	const int32_t nn = node_base;
 	t.n_fast_nodes = std::max(nn, 1);
-	CK(cudaMalloc(&t.d_fast, (size_t)t.n_fast_nodes * sizeof(fast_node)));
+	CK(cudaMallocAsync(&t.d_fast, (size_t)t.n_fast_nodes * sizeof(fast_node), st));
 	if (nn == 0) {
 		k_root_leaf<<<1, 1, 0, st>>>(n, root_box, (fast_node*)t.d_fast);
 	} else {   // breadth-first ids -> the recursive builder's pre-order: sort by (first leaf slot, depth)
@@ -691,7 +696,7 @@ bool fast_bvh_on_device(int32_t n, device_tables& t, cudaStream_t st, plu_build_
 		k_fast_emit<<<blocks(nn), 256, 0, st>>>(nn, perm, newid, nodes, (fast_node*)t.d_fast);
 		CK(cudaStreamSynchronize(st));   // scratch of this scope is freed on return
 	}
-	CK(cudaMalloc(&t.d_fast_leaf, (size_t)n * 12 * sizeof(float)));
+	CK(cudaMallocAsync(&t.d_fast_leaf, (size_t)n * 12 * sizeof(float), st));
 	k_fast_leaf<<<blocks(n), 256, 0, st>>>(n, idx, t.d_prim, t.d_prim_meta, t.d_fast_leaf);
 	CK(cudaStreamSynchronize(st));
 	CK(cudaGetLastError());
@@ -704,7 +709,7 @@ bool fast_bvh_on_device(int32_t n, device_tables& t, cudaStream_t st, plu_build_
 bool build_on_device(const plu_scene_desc* d, device_tables& t, cudaStream_t st, plu_build_stats* stats, std::string& err) {
 	const int32_t n = d->n_prims;
 	if (n <= 0) return true;
-	dev_mem mem;
+	dev_mem mem(st);
 	int32_t* order = mem.get<int32_t>(n);
 	if (!order) { err = "cudaMalloc (leaf order)"; return false; }
 	double t0 = now_ms();

@@ -39,14 +39,17 @@ struct wave_buffers {
 	// (ncu r01e: k_shade read 340 B per vertex for 60 B of payload).
 	//   rec[4*slot+0] = (ray origin, hit_record::t the next scene->hit starts from)
 	//   rec[4*slot+1] = (ray direction, flags)
-	//   rec[4*slot+2] = (path_throughput for even vertices, t of the pending hit)
-	//   rec[4*slot+3] = (path_throughput for odd vertices, surface id of the pending hit)
+	//   rec[4*slot+2] = (path_throughput for even vertices, -)
+	//   rec[4*slot+3] = (path_throughput for odd vertices, -)
 	// path_throughput ping-pongs by vertex parity: k_connect of vertex v still needs T before the vertex.
 	float4* rec;
 	float4* rad;          // L
 	uint32_t* dirty;      // one bit per slot (k_primary): 0 = the camera ray missed, L == 0 and rad[slot] was never written
 	uint32_t* queue[2];   // extend queues, ping-pong
-	uint32_t* q_hit[2];   // paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR)
+	// paths whose extension ray hit, by material class (CLS_DIFFUSE, CLS_SPECULAR): (slot, t, surface, -).  The hit travels IN
+	// the queue entry (written and read as coalesced 16-byte rows) instead of being scattered into the path record, where
+	// two 4-byte stores per ray cost a read-for-ownership of a DRAM sector (ncu r01: k_extend moved 2.7x its bytes)
+	uint4* q_hit[2];
 	float4 *sh_p, *sh_w1, *sh_c1, *sh_w2, *sh_c2;   // shadow entries (one per shaded vertex that needs a connection)
 	uint32_t* counters;   // [bounce*CNT_STRIDE + {CNT_EXTEND, CNT_SHADOW, CNT_HIT_DIFFUSE, CNT_HIT_SPECULAR}]
 	unsigned long long* stats;   // 0 extend rays, 1 shadow rays, 2 nodes visited, 3 prims tested, 4 shaded vertices, 5 shadow entries, 6 graph loop rounds
@@ -141,7 +144,7 @@ PLU_DEV int wave_vertex(const wave_buffers& wb, int b) {
 #define PLU_STAGE_EXTEND (2 * 2 * PLU_CTA * 16)
 #define PLU_STAGE_SHADE_IN (2 * 4 * PLU_CTA * 16)
 #define PLU_STAGE_SHADE (PLU_STAGE_SHADE_IN + 2 * 5 * PLU_CTA * 16)   // + two stages of shadow-entry payload
-#define PLU_STAGE_CONNECT (2 * 5 * PLU_CTA * 16)
+#define PLU_STAGE_CONNECT (2 * 3 * PLU_CTA * 16)
 
 extern __shared__ uint4 plu_smem[];
 
@@ -160,8 +163,8 @@ __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_
 	}
 }
 
-// What k_extend does with the outcome of scene->hit for one path: records the hit in the path record and
-// returns the material class whose queue the path joins (0: the path ends here).
+// What k_extend does with the outcome of scene->hit for one path: returns the material class whose hit queue the path
+// joins with (slot, t, surface) (0: the path ends here).
 //   emission_material: the vertex adds Le (first vertex / after a specular bounce, renderer.cpp:66); its
 //   empty bsdf gives NEE = 0 and sampleF pdf = 0, i.e. the path ends (renderer.cpp:78)
 //   miss: renderer.cpp:87-90, after a specular bounce `L += T * l->Le(r)` with Le == 0 for every light —
@@ -185,9 +188,7 @@ PLU_DEV int extend_finish(const scene_ref& sc, float4* recs, float4* rad, int bo
 			}
 			return 0;
 		}
-		float* rw = (float*)(recs + 4 * (size_t)slot);   // the .w words of quarters 2 and 3
-		rw[11] = t; rw[15] = __int_as_float(prim);
-		return mtag == PLU_MAT_DIFFUSE ? 1 : 2;
+		return mtag == PLU_MAT_DIFFUSE ? 1 : 2;   // the caller queues (slot, t, surface)
 	}
 	if ((flags & (FLAG_SPEC | FLAG_NONFINITE)) == (FLAG_SPEC | FLAG_NONFINITE)) {
 		f3 T = mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]); f3 L = mk3(rad[slot]);
@@ -224,11 +225,9 @@ PLU_DEV int primary_finish(const scene_ref& sc, float4* recs, float4* rad, uint3
 		rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 		return 0;
 	}
-	float4* rec = recs + 4 * (size_t)slot;
+	float4* rec = recs + 4 * (size_t)slot;   // (path_throughput is 1 at the first vertex: its quarters are not read there)
 	rec[0] = make_float4(r.e.x, r.e.y, r.e.z, PLU_T_MAX);
 	rec[1] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(0));
-	rec[2] = make_float4(0.f, 0.f, 0.f, t);
-	rec[3] = make_float4(0.f, 0.f, 0.f, __int_as_float(prim));
 	rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
 	return mtag == PLU_MAT_DIFFUSE ? 1 : 2;
 }
@@ -285,6 +284,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 	__syncthreads();
 	unsigned long long pending = 0;   // leader: result of the group's global atomic of the previous iteration
 	uint32_t pslot = 0, p_ofs_d = 0, p_ofs_s = 0; bool p_d = false, p_s = false;
+	uint32_t p_t = 0, p_prim = 0, c_t = 0, c_prim = 0;   // hit of the previous / current iteration (t as bits)
 	uint32_t buf = 0, it = 0, k3 = 0;
 	unsigned long long* cnt_pair = (unsigned long long*)cnt_diffuse;   // (diffuse, specular) = (low, high)
 	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 				float t; int32_t prim;
 				bool hit = trace_scene<COUNT, SMEM>(sc, r, PLU_T_MAX, t, prim, &tc);
 				int cls = primary_finish(sc, recs, wb.rad, slot, r, hit, t, prim, dirty);
-				to_diffuse = cls == 1; to_specular = cls == 2;
+				to_diffuse = cls == 1; to_specular = cls == 2; c_t = __float_as_uint(t); c_prim = (uint32_t)prim;
 			}
 			// slots of a warp are 32 consecutive, 32-aligned indices: one mask word per warp and iteration
 			const uint32_t mask = __ballot_sync(0xffffffffu, dirty);
@@ -319,15 +319,15 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 			float t; int32_t prim;
 			bool hit = trace_scene<COUNT, SMEM>(sc, r, o.w, t, prim, &tc);
 			int cls = extend_finish(sc, recs, wb.rad, bounce, slot, r, flags, hit, t, prim, nl);
-			to_diffuse = cls == 1; to_specular = cls == 2;
+			to_diffuse = cls == 1; to_specular = cls == 2; c_t = __float_as_uint(t); c_prim = (uint32_t)prim;
 		}
 		warp_tally td, ts; td.add(&s_cnt[grp][k3][0], to_diffuse); ts.add(&s_cnt[grp][k3][1], to_specular);
 		if (leader && it > 0) s_base[grp][(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
 		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
 		if (it > 0) {   // the previous iteration's entries: its global base has arrived meanwhile
 			uint2 gb = s_base[grp][(it - 1u) & 1u];
-			if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
-			if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
+			if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = make_uint4(pslot, p_t, p_prim, 0u);
+			if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = make_uint4(pslot, p_t, p_prim, 0u);
 		}
 		if (leader) {
 			uint32_t cd = s_cnt[grp][k3][0], cs = s_cnt[grp][k3][1];
@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 			uint32_t kz = k3 == 0 ? 2u : k3 - 1u;   // (it + 2) % 3: idle until the iteration after next
 			s_cnt[grp][kz][0] = 0; s_cnt[grp][kz][1] = 0;
 		}
-		p_d = to_diffuse; p_s = to_specular; p_ofs_d = td.ofs; p_ofs_s = ts.ofs; pslot = slot;
+		p_d = to_diffuse; p_s = to_specular; p_ofs_d = td.ofs; p_ofs_s = ts.ofs; pslot = slot; p_t = c_t; p_prim = c_prim;
 		slot = slot_next; slot_next = slot_nn; j = jn; buf ^= 1u;
 		it++; k3 = k3 == 2 ? 0u : k3 + 1u;
 	}
@@ -343,8 +343,8 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 		if (leader) s_base[grp][(it - 1u) & 1u] = make_uint2((uint32_t)pending, (uint32_t)(pending >> 32));
 		if (WARP_SCOPE) __syncwarp(); else __syncthreads();
 		uint2 gb = s_base[grp][(it - 1u) & 1u];
-		if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = pslot;
-		if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = pslot;
+		if (p_d) wb.q_hit[CLS_DIFFUSE][gb.x + p_ofs_d] = make_uint4(pslot, p_t, p_prim, 0u);
+		if (p_s) wb.q_hit[CLS_SPECULAR][gb.y + p_ofs_s] = make_uint4(pslot, p_t, p_prim, 0u);
 	}
 	if (COUNT) {
 		unsigned long long a = tc.nodes, b = tc.prims;
@@ -402,8 +402,9 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend_pt(const __grid_constant_
 			unsigned long long base = 0;
 			if (lane == 0) base = atomicAdd(cnt_pair, ((unsigned long long)__popc(ms) << 32) | (unsigned long long)__popc(md));
 			base = __shfl_sync(FULL, base, 0);
-			if (cls == 1) wb.q_hit[CLS_DIFFUSE][(uint32_t)base + __popc(md & lt)] = slot;
-			if (cls == 2) wb.q_hit[CLS_SPECULAR][(uint32_t)(base >> 32) + __popc(ms & lt)] = slot;
+			const uint4 entry = make_uint4(slot, __float_as_uint(w.best_t), (uint32_t)w.best, 0u);
+			if (cls == 1) wb.q_hit[CLS_DIFFUSE][(uint32_t)base + __popc(md & lt)] = entry;
+			if (cls == 2) wb.q_hit[CLS_SPECULAR][(uint32_t)(base >> 32) + __popc(ms & lt)] = entry;
 		}
 		// refill: idle lanes take consecutive entries of the chunk; a second pass opens the next chunk at a chunk's end
 		for (int pass = 0; pass < 2 && !exhausted; ++pass) {
@@ -455,9 +456,9 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + (CLS == CLS_DIFFUSE ? CNT_HIT_DIFFUSE : CNT_HIT_SPECULAR)];
 	if (blockIdx.x * PLU_CTA >= n) return;   // no work for this CTA: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
-	float4* st_rec = (float4*)stage_base;          // [2][4][PLU_CTA]: the four quarters of the path record
+	float4* st_rec = (float4*)stage_base;          // [2][4][PLU_CTA]: record quarters 0, 1, the incoming throughput, the hit entry
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 4, (unsigned long long)n);
-	const uint32_t* q_in = wb.q_hit[CLS];
+	const uint4* q_in = wb.q_hit[CLS];
 	uint32_t* cnt_shadow = wb.counters + bounce * CNT_STRIDE + CNT_SHADOW;
 	uint32_t* cnt_next = wb.counters + (bounce + 1) * CNT_STRIDE + CNT_EXTEND;
 	uint32_t* q_next = wb.queue[(bounce + 1) & 1];
@@ -465,16 +466,17 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	const float nl = (float)sc.n_lights;
 	const uint32_t q_T_in = 2u + ((uint32_t)bounce & 1u), q_T_out = 2u + (((uint32_t)bounce + 1u) & 1u);
 
-	auto gather = [&](uint32_t b, uint32_t sl) {   // the whole 64-byte record of the slot
+	auto gather = [&](uint32_t b, uint32_t sl, uint32_t jj) {   // ray + incoming throughput of the slot (one 64-byte record), and the hit entry
 		float4* dst = st_rec + (size_t)b * 4 * PLU_CTA + tid;
 		const float4* src = recs + 4 * (size_t)sl;
-		cp_async_16(dst, src); cp_async_16(dst + PLU_CTA, src + 1); cp_async_16(dst + 2 * PLU_CTA, src + 2); cp_async_16(dst + 3 * PLU_CTA, src + 3);
+		cp_async_16(dst, src); cp_async_16(dst + PLU_CTA, src + 1); cp_async_16(dst + 2 * PLU_CTA, src + q_T_in);
+		cp_async_16(dst + 3 * PLU_CTA, q_in + jj);
 	};
 	uint32_t j = blockIdx.x * PLU_CTA + tid;
 	uint32_t slot = 0, slot_next = 0;
-	if (j < n) { slot = q_in[j]; gather(0, slot); }
+	if (j < n) { slot = q_in[j].x; gather(0, slot, j); }
 	cp_async_commit();
-	if (j + stride < n) slot_next = q_in[j + stride];
+	if (j + stride < n) slot_next = q_in[j + stride].x;
 	// CTA-level push state.  Both queues of an iteration (shadow entries, next extend queue) are counted
 	// into shared memory, reserved by ONE thread after the barrier and written in the FOLLOWING iteration;
 	// the shadow payload waits in shared memory meanwhile (st_pay), not in registers.
@@ -502,30 +504,28 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	for (uint32_t base = blockIdx.x * PLU_CTA; base < n; base += stride) {
 		const uint32_t jn = j + stride, jnn = jn + stride;
 		const bool has_next = jn < n;
-		if (has_next) gather(buf ^ 1u, slot_next);
+		if (has_next) gather(buf ^ 1u, slot_next, jn);
 		cp_async_commit();
 		uint32_t slot_nn = 0;
-		if (has_next && jnn < n) slot_nn = q_in[jnn];
+		if (has_next && jnn < n) slot_nn = q_in[jnn].x;
 		cp_async_wait<1>();
 		bool active = j < n, need_entry = false, go_on = false;
 		uint32_t sh_flags = 0;
 		f3 p = mk3(0.f), wi1 = mk3(0.f), c1 = mk3(0.f), wi2 = mk3(0.f), c2 = mk3(0.f);
 		f3 T = mk3(1.f), nrm = mk3(0.f), wo = mk3(0.f);
-		float t = 0.f, hit_w_keep = 0.f; int flags = 0;
+		float t = 0.f; int flags = 0;
 		bsdf b; vertex_rng rng;
 		b.tag = PLU_MAT_DIFFUSE;
 		if (active) {
 			const float4* row = st_rec + (size_t)buf * 4 * PLU_CTA + tid;
-			float4 o4 = row[0], d4 = row[PLU_CTA], q2 = row[2 * PLU_CTA], q3 = row[3 * PLU_CTA];
-			int2 h = make_int2(__float_as_int(q2.w), __float_as_int(q3.w));
-			hit_w_keep = q_T_out == 2u ? q2.w : q3.w;   // the .w of the quarter that receives the new throughput
+			float4 o4 = row[0], d4 = row[PLU_CTA], qT = row[2 * PLU_CTA], he = row[3 * PLU_CTA];
 			ray r; r.e = mk3(o4); r.d = mk3(d4);
 			flags = __float_as_int(d4.w);
-			t = __int_as_float(h.x); int32_t prim = h.y;
+			t = he.y; int32_t prim = __float_as_int(he.z);   // (slot, t, surface, -)
 			int4 meta = sc.prim_meta(prim);   // kind, material, light (-1 here: emissive hits end in k_extend), tie rank
 			const plu_material_desc& m = sc.material(meta.y);
 			hit_rec hr; fill_record(sc, prim, meta.x, r, t, m.texture >= 0, hr);
-			if (bounce != 0) T = q_T_in == 2u ? mk3(q2) : mk3(q3);
+			if (bounce != 0) T = mk3(qT);
 			philox_key key; int32_t px_x, px_y, s;
 			slot_to_path(w, slot, key, px_x, px_y, s);
 			if (CLS == CLS_DIFFUSE) rng.begin(key, bounce);
@@ -621,7 +621,7 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 					float4* rec = recs + 4 * (size_t)slot;
 					rec[0] = make_float4(p.x, p.y, p.z, t);
 					rec[1] = make_float4(wi.x, wi.y, wi.z, __int_as_float(nf));
-					rec[q_T_out] = make_float4(T.x, T.y, T.z, hit_w_keep);
+					rec[q_T_out] = make_float4(T.x, T.y, T.z, 0.f);
 					go_on = true;
 				}
 			}
@@ -663,16 +663,15 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x * PLU_CTA >= n) return;   // no work for this CTA: leave before staging the scene
 	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
-	float4* st = (float4*)stage_base;   // [2][5][PLU_CTA]: p, w1, c1, w2, c2
+	float4* st = (float4*)stage_base;   // [2][3][PLU_CTA]: p, w1, c1 (the rare BSDF-sampled MIS ray's w2, c2 are fetched on demand)
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
 	const float nl = (float)sc.n_lights;
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	uint32_t rays = 0;
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
 	auto gather = [&](uint32_t b, uint32_t jj) {
-		float4* row = st + (size_t)b * 5 * PLU_CTA + tid;
+		float4* row = st + (size_t)b * 3 * PLU_CTA + tid;
 		cp_async_16(row, wb.sh_p + jj); cp_async_16(row + PLU_CTA, wb.sh_w1 + jj); cp_async_16(row + 2 * PLU_CTA, wb.sh_c1 + jj);
-		cp_async_16(row + 3 * PLU_CTA, wb.sh_w2 + jj); cp_async_16(row + 4 * PLU_CTA, wb.sh_c2 + jj);
 	};
 	uint32_t j = blockIdx.x * PLU_CTA + tid, buf = 0;
 	if (j < n) gather(0, j);
@@ -683,7 +682,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 		cp_async_commit();
 		cp_async_wait<1>();
 		if (j < n) {
-			const float4* row = st + (size_t)buf * 5 * PLU_CTA + tid;
+			const float4* row = st + (size_t)buf * 3 * PLU_CTA + tid;
 			float4 p4 = row[0], w1 = row[PLU_CTA];
 			uint32_t slot = __float_as_uint(p4.w), fl = __float_as_uint(w1.w);
 			// path state is only needed after the casts: the loads travel meanwhile
@@ -707,11 +706,14 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
 			}
 			if (fl & SH_NEED2) {
-				r.d = mk3(row[3 * PLU_CTA]);
+				// Li of this term uses the SHADING normal against -wi (renderer.cpp:43), which vanishes for every wi an orthonormal
+				// frame can sample: the entries that carry it are few, so its two rows are not prefetched for every entry
+				const float4 c2 = wb.sh_c2[j];
+				r.d = mk3(wb.sh_w2[j]);
 				float t; int32_t prim;
 				rays++;
 				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc);
-				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(row[4 * PLU_CTA]); any = true; }
+				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(c2); any = true; }
 			}
 			f3 T = mk3(T4);
 			if (any || !finite3(T)) {

@@ -116,6 +116,10 @@ extern "C" int plu_gpu_create(int device, plu_gpu_ctx** out) {
 		}
 	}
 	ctx->sm_count = prop.multiProcessorCount;
+	{   // scene tables and build scratch are stream-ordered allocations: keep the pool's memory between uploads
+		cudaMemPool_t pool = nullptr; uint64_t keep = ~0ull;
+		if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+	}
 	if (const char* e = std::getenv("PLU_PIPES")) { int v = std::atoi(e); if (v >= 1 && v <= PLU_PIPES) ctx->n_pipes = v; }   // tuning knob
 	if (const char* e = std::getenv("PLU_PT_REFILL")) { int v = std::atoi(e); if (v >= 1 && v <= 32) ctx->pt_refill = (uint32_t)v; }   // tuning knob
 	*out = ctx;
@@ -193,9 +197,10 @@ extern "C" int plu_gpu_create_multi(const int* devices, int n_devices, plu_gpu_c
 extern "C" int plu_gpu_device_count(const plu_gpu_ctx* ctx) { return ctx ? 1 + (int)ctx->peers.size() : 0; }
 
 static void free_scene(plu_gpu_ctx* ctx) {
-	cudaFree(ctx->d_blob); cudaFree(ctx->d_tri_uv); cudaFree(ctx->d_tri_normal); cudaFree(ctx->d_texels);
-	cudaFree(ctx->d_walk); ctx->d_walk = nullptr;
-	cudaFree(ctx->d_fast); cudaFree(ctx->d_fast_index); cudaFree(ctx->d_fast_leaf); ctx->d_fast_leaf = nullptr;
+	// scene tables are stream-ordered allocations (see bvh_gpu.cu: dev_mem): no device-wide synchronisation per table
+	void* tables[] = {ctx->d_blob, ctx->d_tri_uv, ctx->d_tri_normal, ctx->d_texels, ctx->d_walk, ctx->d_fast, ctx->d_fast_index, ctx->d_fast_leaf};
+	for (void* t : tables) if (t) cudaFreeAsync(t, ctx->stream);
+	ctx->d_walk = nullptr; ctx->d_fast_leaf = nullptr;
 	ctx->d_blob = nullptr; ctx->d_tri_uv = ctx->d_tri_normal = ctx->d_texels = nullptr; ctx->d_fast = nullptr; ctx->d_fast_index = nullptr;
 	ctx->have_scene = false;
 }
@@ -373,16 +378,16 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 		sc.has_spheres = 1; sc.sphere_rmax = std::max(sc.sphere_rmax, r); sc.sphere_rmin = std::min(sc.sphere_rmin, r);
 	}
 	if (!sc.has_spheres) sc.sphere_rmin = 0.f;
-	CU(cudaMalloc(&ctx->d_blob, blob.size()));
-	CU(cudaMemcpy(ctx->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+	CU(cudaMallocAsync(&ctx->d_blob, blob.size(), ctx->stream));
+	CU(cudaMemcpyAsync(ctx->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice, ctx->stream));
 	sc.blob = ctx->d_blob;
 	if (d->prim_tri_uv && d->prim_tri_normal && n) {
-		CU(cudaMalloc(&ctx->d_tri_uv, n * 6 * sizeof(float))); CU(cudaMemcpy(ctx->d_tri_uv, d->prim_tri_uv, n * 6 * sizeof(float), cudaMemcpyHostToDevice));
-		CU(cudaMalloc(&ctx->d_tri_normal, n * 9 * sizeof(float))); CU(cudaMemcpy(ctx->d_tri_normal, d->prim_tri_normal, n * 9 * sizeof(float), cudaMemcpyHostToDevice));
+		CU(cudaMallocAsync(&ctx->d_tri_uv, n * 6 * sizeof(float), ctx->stream)); CU(cudaMemcpyAsync(ctx->d_tri_uv, d->prim_tri_uv, n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		CU(cudaMallocAsync(&ctx->d_tri_normal, n * 9 * sizeof(float), ctx->stream)); CU(cudaMemcpyAsync(ctx->d_tri_normal, d->prim_tri_normal, n * 9 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	}
 	if (d->image_texels && d->n_image_texels > 0) {
 		size_t bytes = (size_t)d->n_image_texels * 3 * sizeof(float);
-		CU(cudaMalloc(&ctx->d_texels, bytes)); CU(cudaMemcpy(ctx->d_texels, d->image_texels, bytes, cudaMemcpyHostToDevice));
+		CU(cudaMallocAsync(&ctx->d_texels, bytes, ctx->stream)); CU(cudaMemcpyAsync(ctx->d_texels, d->image_texels, bytes, cudaMemcpyHostToDevice, ctx->stream));
 	}
 	sc.tri_uv = ctx->d_tri_uv; sc.tri_normal = ctx->d_tri_normal; sc.texels = ctx->d_texels;
 	if (on_device) {
@@ -391,7 +396,7 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 		tb.d_prim_meta = (int32_t*)(ctx->d_blob + sc.off_prim_meta);
 		tb.d_ref_nodes = ctx->d_blob + sc.off_ref_nodes;
 		std::string berr;
-		CU(cudaDeviceSynchronize());   // the table uploads above went through the default stream; the build runs on ctx->stream
+		CU(cudaStreamSynchronize(ctx->stream));   // the table uploads above are staged from host vectors
 		t0 = wall_ms();
 		bool ok = plubuild::build_on_device(d, tb, ctx->stream, &bs, berr);
 		ctx->d_fast = (fast_node*)tb.d_fast; ctx->d_fast_index = tb.d_fast_index; ctx->d_fast_leaf = (float4*)tb.d_fast_leaf;
@@ -423,10 +428,11 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 				std::memcpy(o + 7, &kr, 4);
 				std::memcpy(kind == PLU_PRIM_SPHERE ? o + 4 : o + 3, &s, 4);
 			}
-			CU(cudaMalloc(&ctx->d_fast_leaf, leaf.size() * sizeof(float)));
-			CU(cudaMemcpy(ctx->d_fast_leaf, leaf.data(), leaf.size() * sizeof(float), cudaMemcpyHostToDevice));
-			CU(cudaMalloc(&ctx->d_fast, fn.size() * sizeof(fast_node))); CU(cudaMemcpy(ctx->d_fast, fn.data(), fn.size() * sizeof(fast_node), cudaMemcpyHostToDevice));
-			CU(cudaMalloc(&ctx->d_fast_index, fi.size() * sizeof(int32_t))); CU(cudaMemcpy(ctx->d_fast_index, fi.data(), fi.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+			CU(cudaMallocAsync(&ctx->d_fast_leaf, leaf.size() * sizeof(float), ctx->stream));
+			CU(cudaMemcpyAsync(ctx->d_fast_leaf, leaf.data(), leaf.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+			CU(cudaMallocAsync(&ctx->d_fast, fn.size() * sizeof(fast_node), ctx->stream)); CU(cudaMemcpyAsync(ctx->d_fast, fn.data(), fn.size() * sizeof(fast_node), cudaMemcpyHostToDevice, ctx->stream));
+			CU(cudaMallocAsync(&ctx->d_fast_index, fi.size() * sizeof(int32_t), ctx->stream)); CU(cudaMemcpyAsync(ctx->d_fast_index, fi.data(), fi.size() * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+			CU(cudaStreamSynchronize(ctx->stream));   // the host vectors go out of scope
 		}
 		sc.n_fast_nodes = (int32_t)fn.size();
 		bs.ms_fast_bvh = wall_ms() - t0; bs.n_fast_nodes = sc.n_fast_nodes;
@@ -447,7 +453,7 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 	if (sc.has_spheres && sc.n_ref_nodes > 0) {   // (small scenes only reach it with PLU_RENDER_BVH_FAST)
 		// sphere::hit is fed non-unit directions, which no walk of the SAH tree can follow: those scenes walk the reference
 		// tree with tight-box pruning instead (isect.cuh: trace_ref_pruned)
-		CU(cudaMalloc(&ctx->d_walk, (size_t)sc.n_ref_nodes * sizeof(walk_node)));
+		CU(cudaMallocAsync(&ctx->d_walk, (size_t)sc.n_ref_nodes * sizeof(walk_node), ctx->stream));
 		const int nb = (sc.n_ref_nodes + 255) / 256;
 		k_walk_init<<<nb, 256, 0, ctx->stream>>>(sc.n_ref_nodes, (const ref_node*)(ctx->d_blob + sc.off_ref_nodes), ctx->d_walk);
 		k_walk_merge<<<(sc.n_prims + 255) / 256, 256, 0, ctx->stream>>>(sc.n_prims, (const float*)(ctx->d_blob + sc.off_prim), (const int32_t*)(ctx->d_blob + sc.off_prim_meta), ctx->d_walk);
@@ -458,7 +464,7 @@ static int upload_single_impl(plu_gpu_ctx* ctx, const plu_scene_desc* d, uint32_
 	}
 	ctx->sc = sc;
 	ctx->blob_in_smem = sc.blob_bytes <= PLU_SMEM_BLOB_MAX;
-	CU(cudaDeviceSynchronize());   // pageable uploads have landed before any stream renders from them
+	CU(cudaStreamSynchronize(ctx->stream));   // uploads and builds have landed before any other stream renders from them
 	ctx->have_scene = true;
 	return PLU_OK;
 }
@@ -502,7 +508,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	CU(cudaFree(ctx->d_wave[P])); ctx->d_wave[P] = nullptr; ctx->cap[P] = 0;
 	size_t N = slots;
 	auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
-	size_t bytes = al(N * 64) + 6 * al(N * 16) + 4 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long)) + al(sizeof(wave_desc)) + al((N + 31) / 32 * 4);
+	size_t bytes = al(N * 64) + 8 * al(N * 16) + 2 * al(N * 4) + al((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t)) + al(8 * sizeof(unsigned long long)) + al(sizeof(wave_desc)) + al((N + 31) / 32 * 4);
 	CU(cudaMalloc(&ctx->d_wave[P], bytes));
 	unsigned char* p = (unsigned char*)ctx->d_wave[P];
 	auto take = [&](size_t b) { unsigned char* r = p; p += al(b); return r; };
@@ -512,7 +518,7 @@ static int ensure_wave(plu_gpu_ctx* ctx, uint32_t slots, int P = 0) {
 	wb.sh_p = (float4*)take(N * 16); wb.sh_w1 = (float4*)take(N * 16); wb.sh_c1 = (float4*)take(N * 16);
 	wb.sh_w2 = (float4*)take(N * 16); wb.sh_c2 = (float4*)take(N * 16);
 	wb.queue[0] = (uint32_t*)take(N * 4); wb.queue[1] = (uint32_t*)take(N * 4);
-	wb.q_hit[0] = (uint32_t*)take(N * 4); wb.q_hit[1] = (uint32_t*)take(N * 4);
+	wb.q_hit[0] = (uint4*)take(N * 16); wb.q_hit[1] = (uint4*)take(N * 16);
 	wb.counters = (uint32_t*)take((PLU_MAX_VERTICES_CAP + 2) * CNT_STRIDE * sizeof(uint32_t));
 	wb.stats = (unsigned long long*)take(8 * sizeof(unsigned long long));
 	wb.desc = (const wave_desc*)take(sizeof(wave_desc));
@@ -1012,14 +1018,14 @@ static int trace_common(plu_gpu_ctx* ctx, int64_t n, const float* o3, const floa
 	select_bvh(ctx, sc, flags);
 	float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr, *d_n = nullptr; int32_t* d_id = nullptr;
 	int rc = PLU_OK;
-	auto cleanup = [&]() { cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_n); cudaFree(d_id); };
+	auto cleanup = [&]() { void* b[] = {d_o, d_d, d_t, d_n, d_id}; for (void* q : b) if (q) cudaFreeAsync(q, ctx->stream); };
 #define CUX(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); cleanup(); return PLU_E_CUDA; } } while (0)
 	if (pw <= 0) {
-		CUX(cudaMalloc(&d_o, (size_t)n * 12)); CUX(cudaMalloc(&d_d, (size_t)n * 12));
+		CUX(cudaMallocAsync(&d_o, (size_t)n * 12, ctx->stream)); CUX(cudaMallocAsync(&d_d, (size_t)n * 12, ctx->stream));
 		CUX(cudaMemcpyAsync(d_o, o3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
 		CUX(cudaMemcpyAsync(d_d, d3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
 	}
-	CUX(cudaMalloc(&d_id, (size_t)n * 4)); CUX(cudaMalloc(&d_t, (size_t)n * 4)); CUX(cudaMalloc(&d_n, (size_t)n * 12));
+	CUX(cudaMallocAsync(&d_id, (size_t)n * 4, ctx->stream)); CUX(cudaMallocAsync(&d_t, (size_t)n * 4, ctx->stream)); CUX(cudaMallocAsync(&d_n, (size_t)n * 12, ctx->stream));
 	int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
 	const bool staged = ctx->blob_in_smem && sc.fast_nodes == nullptr;   // the large-scene walks live in the global-memory kernels
 	if (flags & PLU_RENDER_COUNT_BVH) {
