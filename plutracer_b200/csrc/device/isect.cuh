@@ -10,7 +10,13 @@
 namespace plud {
 
 struct ray { f3 e, d; };
-PLU_DEV f3 ray_at(const ray& r, float t) { return r.e + r.d * t; }
+// ray::operator()(t) = e + d * t (cmmn.h:55): a multiply and an add, each rounded.  The path has no ray epsilon, so whether
+// the next ray re-hits its origin surface at t ~ +0 is decided by the last bit of this point; it is therefore written with
+// explicit round-to-nearest operations that no compiler flag can fuse into an FMA (csrc/shade_tu.cu may be built with
+// -fmad=true: PLU_SHADE_FAST).
+PLU_DEV f3 ray_at(const ray& r, float t) {
+	return mk3(__fadd_rn(r.e.x, __fmul_rn(r.d.x, t)), __fadd_rn(r.e.y, __fmul_rn(r.d.y, t)), __fadd_rn(r.e.z, __fmul_rn(r.d.z, t)));
+}
 
 #define PLU_UNIFORM_WALK_MAX_NODES 64
 #define PLU_T_MAX 100000.f   // hit_record::t initial value, cmmn.h:229

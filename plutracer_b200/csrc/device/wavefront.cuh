@@ -153,7 +153,7 @@ extern __shared__ uint4 plu_smem[];
 // px = pixel + ((sx,sy) + xi*0.999)/n, lens likewise; then camera::generate_ray.  Only waves that extend with k_extend_pt
 // (fast BVH, persistent warps) start here; all others start with k_primary (k_extend<.., PRIMARY>).
 PLU_DEV ray primary_ray(const scene_ref& sc, const wave_desc& w, uint32_t slot);
-__global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb) {
+static __global__ void __launch_bounds__(256) k_generate(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb) {
 	const wave_desc w = *wb.desc;
 	for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < w.n_slots; slot += gridDim.x * blockDim.x) {
 		ray r = primary_ray(sc_in, w, slot);
@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 #define CNT_WORK 24
 #define PT_CHUNK 128u
 #ifndef PT_REFILL
-#define PT_REFILL 12u
+#define PT_REFILL 16u
 #endif
 
 template <bool COUNT, class WALKER = fast_walker>
@@ -735,11 +735,110 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 	}
 }
 
+// ---- k_connect_pt ---------------------------------------------------------------------------------------------
+// k_connect for scenes on the large-scene walks: persistent warps that refill finished lanes, as k_extend_pt (ncu r02a,
+// 1M boxes: k_connect ran at 9.2 of 32 threads per instruction with one entry per lane per iteration — a shadow ray's walk
+// is as uneven as an extension ray's).  A lane holds one shadow entry; its one or two rays (light sample, then the rare
+// BSDF-sampled MIS ray) are walked one after the other, then L += T * (nlights * Ld) as in k_connect.  Same per-entry
+// arithmetic; only the order in which entries are taken differs.
+#define CNT_WORK_CONNECT 25
+template <bool COUNT, class WALKER>
+__global__ void __launch_bounds__(PLU_CTA, 4) k_connect_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
+	constexpr uint32_t FULL = 0xffffffffu;
+	const int bounce = wave_vertex(wb, bounce_arg);
+	float4* const recs = wb.rec;
+	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
+	uint32_t* work = wb.counters + bounce * CNT_STRIDE + CNT_WORK_CONNECT;
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
+	trace_counts tc; tc.nodes = 0; tc.prims = 0;
+	uint32_t rays = 0;
+	const uint32_t lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+	const float nl = (float)sc.n_lights;
+	WALKER w; w.cur = WALKER::DONE; w.sp = 0; w.best = -1; w.best_t = 0.f; w.best_rank = -1;
+	__shared__ int32_t s_stack[PLU_SSTK > 0 ? PLU_SSTK : 1][PLU_SSTK > 0 ? PLU_CTA : 1];
+	walk_stack<PLU_SSTK> stack; stack.sm = &s_stack[0][PLU_SSTK > 0 ? threadIdx.x : 0];
+	bool have = false, exhausted = false, any = false;
+	uint32_t j = 0, fl = 0; int phase = 0;
+	f3 Ld = mk3(0.f);
+	ray r; r.e = mk3(0.f); r.d = mk3(0.f);
+	uint32_t c_next = 0, c_end = 0;
+	for (;;) {
+		// lanes whose walk has ended: visibility rule of the ray, next ray of the entry or the radiance update
+		if (have && w.cur == WALKER::DONE) {
+			const bool hit = w.best >= 0;
+			const int32_t li = (int32_t)(fl >> 8);
+			bool more = false;
+			if (phase == 0) {
+				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
+				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(w.best).z == li)) { Ld = Ld + mk3(wb.sh_c1[j]); any = true; }
+				more = (fl & SH_NEED2) != 0;
+			} else if (hit && sc.prim_meta(w.best).z == li) { Ld = Ld + mk3(wb.sh_c2[j]); any = true; }
+			if (more) {
+				phase = 1; r.d = mk3(wb.sh_w2[j]); rays++;
+				w.template begin_walk<COUNT>(sc, r, &tc);
+			} else {
+				const uint32_t slot = __float_as_uint(wb.sh_p[j].w);
+				const f3 T = bounce == 0 ? mk3(1.f) : mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]);
+				if (any || !finite3(T)) {
+					f3 L = mk3(wb.rad[slot]);
+					L = L + T * (nl * Ld);
+					wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
+				}
+				have = false;
+			}
+		}
+		for (int pass = 0; pass < 2 && !exhausted; ++pass) {
+			const uint32_t idle = __ballot_sync(FULL, !have);
+			if (!idle) break;
+			if (c_next == c_end) {
+				uint32_t b = 0;
+				if (lane == 0) b = atomicAdd(work, PT_CHUNK);
+				b = __shfl_sync(FULL, b, 0);
+				if (b >= n) { exhausted = true; break; }
+				c_next = b; c_end = min(b + PT_CHUNK, n);
+			}
+			const uint32_t idx = c_next + __popc(idle & lt);
+			if (!have && idx < c_end) {
+				j = idx;
+				const float4 p4 = wb.sh_p[j], w1 = wb.sh_w1[j];
+				fl = __float_as_uint(w1.w);
+				r.e = mk3(p4); Ld = mk3(0.f); any = false;
+				if (fl & SH_NEED1) { phase = 0; r.d = mk3(w1); }
+				else { phase = 1; r.d = mk3(wb.sh_w2[j]); }
+				rays++;
+				w.template begin_walk<COUNT>(sc, r, &tc);
+				have = true;
+			}
+			c_next = min(c_next + (uint32_t)__popc(idle), c_end);
+		}
+		if (!__any_sync(FULL, have)) break;
+		const uint32_t min_active = exhausted ? 1u : 33u - refill;
+#if PLU_ANYHIT
+		const bool any_hit = phase == 0 && (fl & SH_DELTA) != 0;   // a point light is visible iff NOTHING is hit: the first hit decides
+#else
+		const bool any_hit = false;
+#endif
+		for (;;) {
+			w.template round<COUNT>(sc, r, stack, &tc, any_hit);
+			if ((uint32_t)__popc(__ballot_sync(FULL, have && w.cur != WALKER::DONE)) < min_active) break;
+		}
+	}
+	unsigned long long a = rays, b = tc.nodes, c = tc.prims;
+	for (int o = 16; o > 0; o >>= 1) {
+		a += __shfl_down_sync(FULL, a, o);
+		if (COUNT) { b += __shfl_down_sync(FULL, b, o); c += __shfl_down_sync(FULL, c, o); }
+	}
+	if (lane == 0) {
+		if (a) atomicAdd(wb.stats + 1, a);
+		if (COUNT) { atomicAdd(wb.stats + 2, b); atomicAdd(wb.stats + 3, c); }
+	}
+}
+
 // ---- k_loop_next ----------------------------------------------------------------------------------------------
 // Last node of the graph's while body: the extension of the next vertex has run; step the loop counter and decide whether
 // another round is needed.  No path is alive when that extension found no surface (its hit queues are empty): every later
 // launch of the wave would find empty queues, so the loop ends there (renderer.cpp:86-91: a miss ends the path).
-__global__ void k_loop_next(const __grid_constant__ wave_buffers wb, cudaGraphConditionalHandle handle) {
+static __global__ void k_loop_next(const __grid_constant__ wave_buffers wb, cudaGraphConditionalHandle handle) {
 	if (threadIdx.x != 0 || blockIdx.x != 0) return;
 	const int mv = wb.desc->max_vertices;
 	uint32_t* loop = wb.counters + (mv + 1) * CNT_STRIDE;
@@ -753,7 +852,7 @@ __global__ void k_loop_next(const __grid_constant__ wave_buffers wb, cudaGraphCo
 // ---- k_accumulate ---------------------------------------------------------------------------------------------
 // target->pixel(floor(px)) += ray_color * smp_wgt, samples in ascending order (renderer.cpp:132).
 // The overflow-column strip (pixel index >= W*H, sampler.h:74-78) lands in pixel (0, row+1).
-__global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb, float* fb, float smp_wgt) {
+static __global__ void __launch_bounds__(256) k_accumulate(const __grid_constant__ wave_desc w, const __grid_constant__ wave_buffers wb, float* fb, float smp_wgt) {
 	for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < (uint32_t)w.npix; q += gridDim.x * blockDim.x) {
 		int32_t pix = w.pix0 + (int32_t)q, wh = w.width * w.height;
 		int32_t dst = pix < wh ? pix : (pix - wh + 1) * w.width;

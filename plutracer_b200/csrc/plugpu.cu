@@ -4,6 +4,7 @@
 // fails with PLU_E_CUDA when no device is usable.
 #include "device/wavefront.cuh"
 #include "device/post.cuh"
+#include "shade_tu.h"
 #include "host/bvh_build.h"
 #include "host/bvh_gpu.h"
 #include "host/scene_store.h"
@@ -539,7 +540,7 @@ static int grid_for(plu_gpu_ctx* ctx, K kernel, size_t smem) {
 }
 
 // dynamic shared memory of a kernel = the staged scene blob (small scenes) + its two cp.async stages
-struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_prim, g_ext_pt, g_shade[2], g_conn, g_acc; };
+struct launch_cfg { bool smem, count, no_pt, no_fork; size_t sm_ext, sm_shade, sm_conn; int g_gen, g_ext, g_prim, g_ext_pt, g_conn_pt, g_shade[2], g_conn, g_acc; };
 
 // Waves of a large scene (fast BVH / pruned reference tree) extend with persistent warps (k_extend_pt) and start with
 // k_generate; all other waves start with k_primary (camera ray generation fused into the first extension).
@@ -552,6 +553,8 @@ static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count, bool force_global = fal
 	c.smem = ctx->blob_in_smem && !force_global; c.count = count; c.no_pt = false; c.no_fork = std::getenv("PLU_NO_FORK") != nullptr;
 	if (ctx->sc.has_spheres) c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true, pruned_walker>, 0) : grid_for(ctx, k_extend_pt<false, pruned_walker>, 0);
 	else c.g_ext_pt = count ? grid_for(ctx, k_extend_pt<true>, 0) : grid_for(ctx, k_extend_pt<false>, 0);
+	if (ctx->sc.has_spheres) c.g_conn_pt = count ? grid_for(ctx, k_connect_pt<true, pruned_walker>, 0) : grid_for(ctx, k_connect_pt<false, pruned_walker>, 0);
+	else c.g_conn_pt = count ? grid_for(ctx, k_connect_pt<true, fast_walker>, 0) : grid_for(ctx, k_connect_pt<false, fast_walker>, 0);
 	size_t blob = c.smem ? ((size_t)ctx->sc.blob_bytes + 127) & ~(size_t)127 : 0;
 	c.sm_ext = blob + PLU_STAGE_EXTEND; c.sm_shade = blob + PLU_STAGE_SHADE; c.sm_conn = blob + PLU_STAGE_CONNECT;
 	c.g_gen = grid_for(ctx, k_generate, 0);
@@ -563,8 +566,8 @@ static launch_cfg make_cfg(plu_gpu_ctx* ctx, bool count, bool force_global = fal
 #undef PICK
 	c.g_prim = c.smem ? (count ? grid_for(ctx, k_extend<true, true, true>, c.sm_ext) : grid_for(ctx, k_extend<true, false, true>, c.sm_ext))
 	                  : (count ? grid_for(ctx, k_extend<false, true, true>, c.sm_ext) : grid_for(ctx, k_extend<false, false, true>, c.sm_ext));
-	c.g_shade[0] = c.smem ? grid_for(ctx, k_shade<true, CLS_DIFFUSE>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_DIFFUSE>, c.sm_shade);
-	c.g_shade[1] = c.smem ? grid_for(ctx, k_shade<true, CLS_SPECULAR>, c.sm_shade) : grid_for(ctx, k_shade<false, CLS_SPECULAR>, c.sm_shade);
+	c.g_shade[0] = ctx->sm_count * plushade::max_blocks_per_sm(c.smem, CLS_DIFFUSE, c.sm_shade);   // (k_shade lives in shade_tu.cu)
+	c.g_shade[1] = ctx->sm_count * plushade::max_blocks_per_sm(c.smem, CLS_SPECULAR, c.sm_shade);
 	return c;
 }
 
@@ -642,18 +645,20 @@ static int launch_shade_connect(plu_gpu_ctx* ctx, const scene_ref& sc, const lau
 	const bool fork = ctx->has_specular && !pf->on && !c.no_fork;
 	int launches = 2;
 	if (fork) cudaEventRecord(ctx->ev_fork[P], st);
-	if (c.smem) k_shade<true, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
-	else k_shade<false, CLS_DIFFUSE><<<c.g_shade[0], PLU_CTA, c.sm_shade, st>>>(sc, wb, b);
+	plushade::launch(c.smem, CLS_DIFFUSE, c.g_shade[0], c.sm_shade, st, sc, wb, b);
 	if (ctx->has_specular) {
 		cudaStream_t s2 = fork ? ctx->aux[P] : st;
 		if (fork) cudaStreamWaitEvent(s2, ctx->ev_fork[P], 0);
-		if (c.smem) k_shade<true, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b);
-		else k_shade<false, CLS_SPECULAR><<<c.g_shade[1], PLU_CTA, c.sm_shade, s2>>>(sc, wb, b);
+		plushade::launch(c.smem, CLS_SPECULAR, c.g_shade[1], c.sm_shade, s2, sc, wb, b);
 		launches++;
 		if (fork) { cudaEventRecord(ctx->ev_join[P], s2); cudaStreamWaitEvent(st, ctx->ev_join[P], 0); }
 	}
 	pf->mark(2, st);
-	if (c.smem) { if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
+	if (wave_uses_pt(sc, c) && std::getenv("PLU_NO_CONNECT_PT") == nullptr) {   // large-scene walks: persistent warps with lane refill
+		if (sc.has_spheres) { if (c.count) k_connect_pt<true, pruned_walker><<<c.g_conn_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill); else k_connect_pt<false, pruned_walker><<<c.g_conn_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill); }
+		else { if (c.count) k_connect_pt<true, fast_walker><<<c.g_conn_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill); else k_connect_pt<false, fast_walker><<<c.g_conn_pt, PLU_CTA, 0, st>>>(sc, wb, b, ctx->pt_refill); }
+	}
+	else if (c.smem) { if (c.count) k_connect<true, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<true, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
 	else if (sc.fast_nodes == nullptr) { if (c.count) k_connect<false, true><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
 	else if (sc.has_spheres) { if (c.count) k_connect<false, true, PLU_WALKS_PRUNED><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false, PLU_WALKS_PRUNED><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
 	else { if (c.count) k_connect<false, true, PLU_WALKS_FAST><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); else k_connect<false, false, PLU_WALKS_FAST><<<c.g_conn, PLU_CTA, c.sm_conn, st>>>(sc, wb, b); }
