@@ -297,6 +297,25 @@ int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t width, int32_t height, const fl
 int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t width, int32_t height, const float* d_rgb,
                               uint32_t flags, void* stream, unsigned char* out_bmp, int64_t cap);
 
+/* plu_gpu_encode_bmp_device WITHOUT ANY ALLOCATION.  This entry point has no counterpart in the
+ * reference: it was added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same bytes as plu_gpu_encode_bmp_device, but the .bmp body is staged in a
+ * fixed device array inside the library instead of a buffer allocated and freed per call: the
+ * call makes no cudaMalloc / cudaFree and no allocating library call.
+ *   limit     the body (plu_bmp_size(w, h) - 54 bytes) must fit PLU_NOALLOC_BMP_MAX_BODY (8 MiB:
+ *             up to 1920 x 1080); larger images are rejected with PLU_E_ARG and a message.
+ *   cost      every GPU that loads libplugpu holds those 8 MiB until the process exits.
+ *   sharing   ALL calls on a device share the one array, which keeps the last call's bytes (each
+ *             call overwrites every byte it then reads back, so nothing needs clearing): calls
+ *             that overlap on the GPU (different streams or contexts on one device) RACE — keep
+ *             them on one stream or serialise them.  The call synchronises `stream` before
+ *             returning, as plu_gpu_encode_bmp_device does.                                     */
+#define PLU_NOALLOC_BMP_MAX_BODY (8u << 20)
+int plu_gpu_encode_bmp_device_noalloc(plu_gpu_ctx* ctx, int32_t width, int32_t height,
+                                      const float* d_rgb, uint32_t flags, void* stream,
+                                      unsigned char* out_bmp, int64_t cap);
+
 /* The context keeps the image of its last plu_gpu_render on its (first) device.  These two run
  * the steps after the path on that RESIDENT framebuffer, so the float pixels cross PCIe once
  * (the render's own download) instead of once per step: tone map in place on the device

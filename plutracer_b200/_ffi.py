@@ -20,6 +20,7 @@ RENDER_PROFILE = 16
 RENDER_NO_LANE_REFILL = 32
 POST_TONEMAP = 1
 ABI_VERSION = 2
+NOALLOC_BMP_MAX_BODY = 8 << 20
 
 
 class CameraDesc(C.Structure):
@@ -98,6 +99,7 @@ SYMBOLS = {
     "plu_bmp_size": (C.c_int64, [C.c_int32, C.c_int32]),
     "plu_gpu_encode_bmp": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, C.c_int64]),
     "plu_gpu_encode_bmp_device": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, _P, C.c_int64]),
+    "plu_gpu_encode_bmp_device_noalloc": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, _P, C.c_int64]),
     "plu_gpu_postprocess_resident": (C.c_int, [_P, _P]),
     "plu_gpu_encode_bmp_resident": (C.c_int, [_P, C.c_uint32, _P, C.c_int64]),
     "plu_scene_load_urn": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.POINTER(_P), C.c_char_p, C.c_int]),

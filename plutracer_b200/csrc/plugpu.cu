@@ -1174,6 +1174,57 @@ extern "C" int plu_gpu_encode_bmp_device(plu_gpu_ctx* ctx, int32_t w, int32_t h,
 	return PLU_OK;
 }
 
+// ---- plu_gpu_encode_bmp_device without any allocation (include/plugpu.h: PLU_NOALLOC_BMP_MAX_BODY) ----------------------
+// The .bmp body of plu_gpu_encode_bmp_device goes through a scratch buffer that call cudaMallocs and frees; callers that
+// must not allocate get the same kernel on a FIXED scratch: a file-scope device array of a stated maximum size.  Every GPU
+// that loads the library holds these bytes until the process exits.  `g_noalloc_bmp_body` below is, in host code, only a
+// host-side stand-in for the array (not a device address): its device address is taken ONCE PER DEVICE, with that device
+// current, by cudaGetSymbolAddress, and that pointer is what the kernel receives.
+static __device__ __align__(256) unsigned char g_noalloc_bmp_body[PLU_NOALLOC_BMP_MAX_BODY];
+
+#define PLU_NOALLOC_MAX_DEVICES 64
+static int noalloc_bmp_scratch(plu_gpu_ctx* ctx, unsigned char** out) {   // caller has made ctx->device current
+	static std::mutex mu;
+	static unsigned char* ptr[PLU_NOALLOC_MAX_DEVICES] = {};   // per device: the array is one object per GPU
+	if (ctx->device < 0 || ctx->device >= PLU_NOALLOC_MAX_DEVICES) return fail(ctx, PLU_E_ARG, "device index beyond the no-allocation scratch table");
+	std::lock_guard<std::mutex> lock(mu);
+	if (!ptr[ctx->device]) {
+		void* q = nullptr;
+		cudaError_t e = cudaGetSymbolAddress(&q, g_noalloc_bmp_body);
+		if (e != cudaSuccess || !q) return fail(ctx, PLU_E_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_bmp_body): ") + cudaGetErrorString(e));
+		ptr[ctx->device] = (unsigned char*)q;
+	}
+	*out = ptr[ctx->device];
+	return PLU_OK;
+}
+
+extern "C" int plu_gpu_encode_bmp_device_noalloc(plu_gpu_ctx* ctx, int32_t w, int32_t h, const float* d_rgb, uint32_t flags, void* stream,
+                                                 unsigned char* out, int64_t cap) {
+	if (!ctx) return PLU_E_ARG;
+	if (w <= 0 || h <= 0 || !d_rgb || !out) return fail(ctx, PLU_E_ARG, "bad image arguments");
+	const int64_t total = plu_bmp_size(w, h);
+	if (cap < total) return fail(ctx, PLU_E_ARG, "output buffer smaller than plu_bmp_size");
+	if (total - 54 > (int64_t)PLU_NOALLOC_BMP_MAX_BODY)
+		return fail(ctx, PLU_E_ARG, "image too large for the no-allocation entry point: its .bmp body (" + std::to_string(total - 54) +
+		            " bytes) exceeds PLU_NOALLOC_BMP_MAX_BODY (" + std::to_string((long long)PLU_NOALLOC_BMP_MAX_BODY) + "); use plu_gpu_encode_bmp_device");
+	CU(cudaSetDevice(ctx->device));
+	unsigned char* d_body = nullptr;
+	int rc = noalloc_bmp_scratch(ctx, &d_body);
+	if (rc != PLU_OK) return rc;
+	cudaStream_t st = stream ? (cudaStream_t)stream : cudaStreamLegacy;
+	const int64_t n = (int64_t)w * h;
+	const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+	// the array keeps the previous call's bytes; nothing has to start at zero: k_encode_bmp writes EVERY byte of the
+	// total - 54 it is given (pixels and the zero padding of each row), and only those are copied out
+	k_encode_bmp<<<grid, 256, 0, st>>>(w, h, d_rgb, (flags & PLU_POST_TONEMAP) ? 1 : 0, d_body);
+	cudaError_t e = cudaGetLastError();
+	if (e == cudaSuccess) e = cudaMemcpyAsync(out + 54, d_body, (size_t)(total - 54), cudaMemcpyDeviceToHost, st);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+	if (e != cudaSuccess) return fail(ctx, PLU_E_CUDA, std::string("bmp encode (no allocation): ") + cudaGetErrorString(e));
+	bmp_header(w, h, out);
+	return PLU_OK;
+}
+
 extern "C" int plu_gpu_encode_bmp(plu_gpu_ctx* ctx, int32_t w, int32_t h, const float* rgb, uint32_t flags, unsigned char* out, int64_t cap) {
 	if (!ctx) return PLU_E_ARG;
 	if (w <= 0 || h <= 0 || !rgb || !out) return fail(ctx, PLU_E_ARG, "bad image arguments");
