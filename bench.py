@@ -164,7 +164,9 @@ def measured_traffic(config, kernel):
     try:
         fn = "traffic.json" if config == DEFAULT_CONFIG else f"traffic_{config}.json"
         with open(os.path.join(ROOT, "profiles", fn)) as f:
-            e = json.load(f)[kernel]
+            t = json.load(f)
+        # large scenes extend / connect with the persistent-warp kernels: the capture lists them under their own names
+        e = t[kernel] if kernel in t else t[kernel + "_pt"]
         keys = ("issue_active_pct", "threads_per_instruction", "warps_active_pct", "dram_throughput_pct", "l2_read_gbs", "dram_read_gbs", "l1_hit_pct", "l2_hit_pct")
         return float(e["dram_bytes_per_launch"]), e.get("source", "profiles/" + fn), {k: e[k] for k in keys if k in e}
     except Exception:
