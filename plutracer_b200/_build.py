@@ -22,7 +22,7 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 def lib_path(flavour=None):
     flavour = os.environ.get("PLU_LIB", "") if flavour is None else flavour
-    return os.path.join(LIB_DIR, "libplugpu_shadefast.so" if flavour == "shadefast" else "libplugpu.so")
+    return os.path.join(LIB_DIR, f"libplugpu_{flavour}.so" if flavour else "libplugpu.so")   # PLU_LIB=shadefast, or an A/B build
 
 
 LIB_PATH = lib_path()
@@ -35,6 +35,8 @@ COMMON = [
     *(["-DPLU_LEAF_SMALL=" + os.environ["PLU_LEAF_SMALL"]] if os.environ.get("PLU_LEAF_SMALL") else []),
     *(["-DPLU_SSTK=" + os.environ["PLU_SSTK"]] if os.environ.get("PLU_SSTK") else []),
     *(["-DPLU_ANYHIT=" + os.environ["PLU_ANYHIT"]] if os.environ.get("PLU_ANYHIT") else []),
+    *(["-DPLU_PREFETCH_FAR=" + os.environ["PLU_PREFETCH_FAR"]] if os.environ.get("PLU_PREFETCH_FAR") else []),
+    *(["-DPLU_PT_BLOCKS=" + os.environ["PLU_PT_BLOCKS"]] if os.environ.get("PLU_PT_BLOCKS") else []),
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread",
 ]
 

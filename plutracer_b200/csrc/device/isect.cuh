@@ -288,6 +288,9 @@ PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, 
 #define PLU_SSTK 8
 #endif
 #define PLU_WALK_CTA 256   // == PLU_CTA and k_trace_rays' block size
+#ifndef PLU_PREFETCH_FAR
+#define PLU_PREFETCH_FAR 0
+#endif
 // Capacity: both builders split by SAH down to depth 40 and halve the surface count from there on (host/bvh_build.cpp,
 // bvh_gpu.cu), so a tree over n surfaces is at most 41 + ceil(log2 n) <= PLU_WALK_DEPTH_MAX levels deep for every int32
 // n, and the walks push at most one entry per level; plu_gpu_upload_scene re-checks the bound against the built tree.
@@ -334,7 +337,12 @@ struct fast_walker {
 		bool h1 = !(f1 < n1) && !(f1 < 0.f) && !(n1 > cull);
 		if (h0 && h1) {
 			bool first1 = n1 < n0;
-			stack.push(sp++, first1 ? d.x : d.y);
+			const int32_t far = first1 ? d.x : d.y;
+			stack.push(sp++, far);
+#if PLU_PREFETCH_FAR
+			// experiment (profiles/r02_summary.md 6): request the stacked child now, so that it is in L1 / L2 when the walk returns to it
+			if (far >= 0) { const char* q = (const char*)(nodes + far); asm volatile("prefetch.global.L2 [%0];" ::"l"(q)); }
+#endif
 			cur = first1 ? d.y : d.x;
 		} else if (h0) cur = d.x;
 		else if (h1) cur = d.y;

@@ -369,8 +369,11 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 #define PT_REFILL 16u
 #endif
 
+#ifndef PLU_PT_BLOCKS
+#define PLU_PT_BLOCKS 4   // resident CTAs per SM the persistent-warp kernels are compiled for (4: 64 registers)
+#endif
 template <bool COUNT, class WALKER = fast_walker>
-__global__ void __launch_bounds__(PLU_CTA, 4) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
+__global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_extend_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	const int bounce = wave_vertex(wb, bounce_arg);
 	float4* const recs = wb.rec;
@@ -743,7 +746,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 // arithmetic; only the order in which entries are taken differs.
 #define CNT_WORK_CONNECT 25
 template <bool COUNT, class WALKER>
-__global__ void __launch_bounds__(PLU_CTA, 4) k_connect_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
+__global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_connect_pt(const __grid_constant__ scene_ref sc, const __grid_constant__ wave_buffers wb, int bounce_arg, uint32_t refill) {
 	constexpr uint32_t FULL = 0xffffffffu;
 	const int bounce = wave_vertex(wb, bounce_arg);
 	float4* const recs = wb.rec;
