@@ -370,25 +370,38 @@ struct fast_walker {
 	// any_hit: the caller only asks WHETHER a surface is hit (point-light visibility, renderer.cpp:17 with
 	// is_delta()): the first hit ends the walk.  Whether a hit exists does not depend on the visiting order, and
 	// distance culling only starts after a first hit, so the answer is the closest-hit walk's.
+	// keep >= 0: the walk was SEEDED with the hit of surface `keep` (seed(): an area light's own surface, whose hit distance the
+	// caller computed with the same prim_t) and the caller only asks whether that surface is the closest hit (renderer.cpp:17,
+	// :42): culling starts at the seed's distance and the walk ends as soon as anything replaces it under the same
+	// (t, tie rank) rule — what replaced it need not be the closest hit, the answer "not the light" is already final.
 	template <bool COUNT, class STK>
-	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
+	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false, int32_t keep = -1) {
 		const fast_node* nodes = sc.fast_nodes;
 		while (cur >= 0) node_step<COUNT>(nodes, stack, tc);
 		if (cur == DONE) return;
 		leaf_test<COUNT>(sc.fast_leaf, r, cur, tc);
-		if (sp > 0 && !(any_hit && best >= 0)) cur = stack.pop(--sp); else cur = DONE;
+		const bool stop = (any_hit && best >= 0) || (keep >= 0 && best != keep);
+		if (sp > 0 && !stop) cur = stack.pop(--sp); else cur = DONE;
 	}
+	static constexpr bool CAN_SEED = true;
+	PLU_DEV void seed(float t, int32_t prim, int32_t rank) { best_t = t; best = prim; best_rank = rank; }
 };
 
 template <bool COUNT, int S>
-PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit) {
+PLU_DEV bool trace_fast(const scene_ref& sc, const ray& r, float& t_out, int32_t& prim_out, trace_counts* tc, bool any_hit, int32_t light_prim = -1) {
 	fast_walker w; w.begin(sc, r);
+	int32_t keep = -1;
+	if (light_prim >= 0) {   // "is the light's surface the closest hit": seeded walk, see fast_walker::round
+		const int4 lm = sc.prim_meta(light_prim);
+		float tl;
+		if (prim_t(sc, light_prim, lm.x, r, PLU_T_MAX, tl)) { w.seed(tl, light_prim, lm.w); keep = light_prim; }
+	}
 	__shared__ int32_t s_stack[S > 0 ? S : 1][S > 0 ? PLU_WALK_CTA : 1];
 	walk_stack<S> stack; stack.sm = &s_stack[0][S > 0 ? threadIdx.x : 0];
 	// "while-while" walk: every lane first descends to its next leaf, then the warp tests leaves together;
 	// with one if/else per step (r01f: 8.6 of 32 threads active per instruction) node and leaf work of
 	// different lanes alternated serially
-	while (w.cur != fast_walker::DONE) w.round<COUNT>(sc, r, stack, tc, any_hit);
+	while (w.cur != fast_walker::DONE) w.round<COUNT>(sc, r, stack, tc, any_hit, keep);
 	t_out = w.best_t; prim_out = w.best;
 	return w.best >= 0;
 }
@@ -511,8 +524,12 @@ struct pruned_walker : general_walker {
 		}
 	}
 	// one round: expand the interior node `cur` (both children: leaves are tested, interior ones ranked), move on
+	// (never seeded: the reference reaches the light's leaf only through ancestors that pass ITS slab test, which the seed
+	// would assume)
+	static constexpr bool CAN_SEED = false;
+	PLU_DEV void seed(float, int32_t, int32_t) {}
 	template <bool COUNT, class STK>
-	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false) {
+	PLU_DEV void round(const scene_ref& sc, const ray& r, STK& stack, trace_counts* tc, bool any_hit = false, int32_t = -1) {
 		if (cur == DONE) return;
 		const int32_t k = __float_as_int(__ldg(&sc.walk_nodes[cur].c).w);
 		const int32_t kl = k >> 1, L = cur + 1, R = cur + 2 * kl;
@@ -557,10 +574,12 @@ PLU_DEV bool trace_ref_pruned(const scene_ref& sc, const ray& r, float& t_out, i
 #define PLU_WALKS_FAST 1     // sphere-free scene: the SAH tree
 #define PLU_WALKS_PRUNED 2   // scene with spheres: the pruned reference tree
 template <bool COUNT, bool SMEM, int WALKS = PLU_WALKS_BOTH>
-PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc, bool any_hit = false) {
+// light_prim >= 0: the caller only asks whether that surface (an area light's) is the closest hit; walks that can answer
+// without finding the closest hit do (the SAH tree), the others ignore it — the returned surface is the light's iff it is.
+PLU_DEV bool trace_scene(const scene_ref& sc, const ray& r, float root_bound, float& t, int32_t& prim, trace_counts* tc, bool any_hit = false, int32_t light_prim = -1) {
 	if (!SMEM && sc.fast_nodes != nullptr) {
 		if (WALKS == PLU_WALKS_PRUNED || (WALKS == PLU_WALKS_BOTH && sc.has_spheres)) return trace_ref_pruned<COUNT, PLU_SSTK>(sc, r, t, prim, tc, any_hit);
-		return trace_fast<COUNT, PLU_SSTK>(sc, r, t, prim, tc, any_hit);
+		return trace_fast<COUNT, PLU_SSTK>(sc, r, t, prim, tc, any_hit, light_prim);
 	}
 	if (sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES) return trace_ref_uniform<COUNT, SMEM>(sc, r, root_bound, t, prim, tc);
 	return trace_ref<COUNT>(sc, r, root_bound, t, prim, tc);

@@ -654,6 +654,9 @@ __global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ sc
 	}
 }
 
+#ifndef PLU_SEED_AREA
+#define PLU_SEED_AREA 1   // 1: area-light shadow rays on the SAH tree end at the first surface that beats the light's own hit
+#endif
 // ---- k_connect ------------------------------------------------------------------------------------------------
 // The scene->hit calls of estimate_direct_light (renderer.cpp:16,41) and the radiance update
 // `L += path_throughput * (nlights * Ld)` (renderer.cpp:56,74).
@@ -672,6 +675,13 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 	trace_counts tc; tc.nodes = 0; tc.prims = 0;
 	uint32_t rays = 0;
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, stride = gridDim.x * PLU_CTA;
+	auto seed_prim = [&](int32_t light) -> int32_t {   // surface of an area light for the seeded walk (k_connect_pt does the same)
+#if PLU_SEED_AREA
+		return (!SMEM && light >= 0) ? sc.light(light).prim : -1;
+#else
+		return -1;
+#endif
+	};
 	auto gather = [&](uint32_t b, uint32_t jj) {
 		float4* row = st + (size_t)b * 3 * PLU_CTA + tid;
 		cp_async_16(row, wb.sh_p + jj); cp_async_16(row + PLU_CTA, wb.sh_w1 + jj); cp_async_16(row + 2 * PLU_CTA, wb.sh_c1 + jj);
@@ -704,7 +714,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 #else
 				const bool any_hit = false;
 #endif
-				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc, any_hit);
+				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc, any_hit, seed_prim(fl & SH_DELTA ? -1 : li));
 				// visible: nothing hit, or (area light) the surface hit is the light's own (renderer.cpp:17)
 				if (!hit || (!(fl & SH_DELTA) && sc.prim_meta(prim).z == li)) { Ld = Ld + mk3(row[2 * PLU_CTA]); any = true; }
 			}
@@ -715,7 +725,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 				r.d = mk3(wb.sh_w2[j]);
 				float t; int32_t prim;
 				rays++;
-				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc);
+				bool hit = trace_scene<COUNT, SMEM, WALKS>(sc, r, PLU_T_MAX, t, prim, &tc, false, seed_prim(li));
 				if (hit && sc.prim_meta(prim).z == li) { Ld = Ld + mk3(c2); any = true; }
 			}
 			f3 T = mk3(T4);
@@ -764,6 +774,20 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_connect_pt(const __g
 	uint32_t j = 0, fl = 0; int phase = 0;
 	f3 Ld = mk3(0.f);
 	ray r; r.e = mk3(0.f); r.d = mk3(0.f);
+	int32_t keep = -1;   // surface the current walk was seeded with (an area light's own surface), -1: closest-hit walk
+	// start the walk of the lane's current ray; area-light rays on the SAH tree are seeded with the light surface's own hit
+	auto start_ray = [&]() {
+		w.template begin_walk<COUNT>(sc, r, &tc);
+		keep = -1;
+#if PLU_SEED_AREA
+		if (WALKER::CAN_SEED && !(phase == 0 && (fl & SH_DELTA))) {
+			const int32_t lp = sc.light((int32_t)(fl >> 8)).prim;
+			const int4 lm = sc.prim_meta(lp);
+			float tl;
+			if (prim_t(sc, lp, lm.x, r, PLU_T_MAX, tl)) { w.seed(tl, lp, lm.w); keep = lp; }
+		}
+#endif
+	};
 	uint32_t c_next = 0, c_end = 0;
 	for (;;) {
 		// lanes whose walk has ended: visibility rule of the ray, next ray of the entry or the radiance update
@@ -778,7 +802,7 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_connect_pt(const __g
 			} else if (hit && sc.prim_meta(w.best).z == li) { Ld = Ld + mk3(wb.sh_c2[j]); any = true; }
 			if (more) {
 				phase = 1; r.d = mk3(wb.sh_w2[j]); rays++;
-				w.template begin_walk<COUNT>(sc, r, &tc);
+				start_ray();
 			} else {
 				const uint32_t slot = __float_as_uint(wb.sh_p[j].w);
 				const f3 T = bounce == 0 ? mk3(1.f) : mk3(recs[4 * (size_t)slot + 2 + (bounce & 1)]);
@@ -809,7 +833,7 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_connect_pt(const __g
 				if (fl & SH_NEED1) { phase = 0; r.d = mk3(w1); }
 				else { phase = 1; r.d = mk3(wb.sh_w2[j]); }
 				rays++;
-				w.template begin_walk<COUNT>(sc, r, &tc);
+				start_ray();
 				have = true;
 			}
 			c_next = min(c_next + (uint32_t)__popc(idle), c_end);
@@ -822,7 +846,7 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_connect_pt(const __g
 		const bool any_hit = false;
 #endif
 		for (;;) {
-			w.template round<COUNT>(sc, r, stack, &tc, any_hit);
+			w.template round<COUNT>(sc, r, stack, &tc, any_hit, keep);
 			if ((uint32_t)__popc(__ballot_sync(FULL, have && w.cur != WALKER::DONE)) < min_active) break;
 		}
 	}

@@ -89,8 +89,11 @@ class Oracle:
         planes = b6[inner]
         bad = np.zeros(len(o), bool)
         for k in range(3):
-            on_plane = (o[:, k, None] == planes[None, :, k]) | (o[:, k, None] == planes[None, :, 3 + k])
-            bad |= (d[:, k] == 0) & on_plane.any(axis=1)
+            zero = np.flatnonzero(d[:, k] == 0)   # only these rays can evaluate 0 * inf on axis k
+            if zero.size == 0:
+                continue
+            vals = np.unique(np.concatenate([planes[:, k], planes[:, 3 + k]]))
+            bad[zero] |= np.isin(o[zero, k], vals)
         return bad
 
     def sample_radiance(self, scene, params, pixel_begin, pixel_count, trig=0):

@@ -402,3 +402,34 @@ def test_graph_replay_and_wave_size_do_not_change_the_image(lib, name, monkeypat
         assert same_bits(out[0][0], img).all()
         assert (st.samples, st.rays_extend, st.rays_shadow, st.shade_vertices) == (out[0][1].samples, out[0][1].rays_extend, out[0][1].rays_shadow, out[0][1].shade_vertices)
     assert out[0][1].waves < out[3][1].waves   # the adapted render used larger waves
+
+
+def test_fast_walks_equal_the_reference_tree_on_the_million_surface_scenes(gpu, oracle):
+    """BASELINE configs[4] at ITS size (10^6 surfaces): the exhaustive walk of the reference's own tree
+    (PLU_RENDER_BVH_REFERENCE: ~2 x 10^6 nodes per ray) against the shipped walks — the SAH tree for boxes + triangles, the
+    pruned reference tree for spheres — on camera rays and on rays from inside the lattice incl. non-unit directions.
+    The count of unmasked rays that differ must be 0 (masked: rays with d_k == 0 whose origin lies on a plane of one of the
+    reference's node boxes, 0 * inf — counted)."""
+    from tools.gen_synth import make_scene
+    rng = np.random.default_rng(31)
+    n_rays = 3000
+    ro = rng.uniform(-55, 55, (n_rays, 3)).astype(np.float32)
+    rd = rng.normal(size=(n_rays, 3)).astype(np.float32)
+    rd /= np.linalg.norm(rd, axis=1, keepdims=True)
+    rd[:600] *= rng.uniform(0.3, 2.0, (600, 1)).astype(np.float32)                                   # non-unit
+    rd[600:900] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 300)] * rng.choice([-1.0, 1.0], (300, 1)).astype(np.float32)   # axis-aligned
+    ro[900:1200] = np.array([0, 0, -140], np.float32)                                               # from the camera
+    rd[900:1200] = rd[900:1200] * 0.2 + np.array([0, 0, 1], np.float32)
+    rd[900:1200] /= np.linalg.norm(rd[900:1200], axis=1, keepdims=True)
+    out = {}
+    for kind in ("mixed", "spheres"):
+        sc = make_scene(1000000, seed=1, kind=kind, width=64, height=64, n_strata=1)
+        gpu.upload(sc)
+        x = gpu.trace_rays(ro, rd, REF)
+        y = gpu.trace_rays(ro, rd, 0)
+        keep = ~oracle.nan_slab_rays(sc, ro, rd)
+        differ = int(((x[0] != y[0]) | ~same_bits(x[1], y[1]))[keep].sum())
+        out[kind] = {"rays": n_rays, "masked": int((~keep).sum()), "hits": int((x[0] >= 0).sum()), "unmasked_rays_that_differ": differ}
+        assert keep.mean() > 0.98 and (x[0] >= 0).mean() > 0.3
+        assert differ == 0, out
+    record_parity("gpu:synthetic-1M:REF-vs-shipped-walk", out)
