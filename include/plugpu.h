@@ -212,6 +212,11 @@ const char* plu_gpu_last_error(const plu_gpu_ctx* ctx);
 /* Deep-copy the tables to the device, build the traversal structure.  Replaces scene->hit,
  * the material/light/texture object graphs and bvh_tree construction (main.cpp:168-171).        */
 int plu_gpu_upload_scene(plu_gpu_ctx* ctx, const plu_scene_desc* scene);
+/* The context remembers the tables it was given: uploading a scene whose surfaces, materials,
+ * textures, lights and tie ranks are byte for byte those already on the device (only the camera
+ * may differ) returns at once and keeps the traversal structures — a caller that flattens and
+ * uploads before every render (the C++ drop-in: the object graph may have changed) pays for a
+ * rebuild only when something did.  plu_build_stats.reserved == 1 then, ms_total == 0.           */
 
 /* Where the traversal structures are built.  The reference builds its tree on the host with a
  * recursive median split (bvh_tree.cpp:7-36: round-robin axis, std::sort by box centre, halves);

@@ -89,3 +89,55 @@ def test_empty_object_list(gpu, tmp_path):
     assert st.samples == 64 and not img.any()
     ids, t, nrm = gpu.trace_primary(8, 8)
     assert (ids == -1).all()
+
+
+@pytest.mark.gpu
+def test_upload_of_an_unchanged_scene_keeps_the_device_tables(lib, tmp_path):
+    """plu_gpu_upload_scene compares the tables it is given with those on the device, byte for byte: the same scene again
+    (what the C++ drop-in does before every render) rebuilds nothing (plu_build_stats.reserved == 1); a camera-only change
+    keeps the structures and takes the new camera; any other change rebuilds.  Images always equal a fresh context's."""
+    from plutracer_b200 import GpuContext, Scene, _ffi
+    w, h, n = 48, 36, 3
+    sc = _load(tmp_path, "sphere-light", w, h, n)
+    p = GpuContext.params(w, h, n, seed=4)
+
+    def fresh(scene):
+        c = GpuContext(0)
+        try:
+            c.upload(scene)
+            img = np.zeros((h, w, 3), np.float32)
+            c.render(p, img)
+            return img
+        finally:
+            c.close()
+
+    ctx = GpuContext(0)
+    try:
+        assert ctx.upload(sc).reserved == 0
+        a = np.zeros((h, w, 3), np.float32); ctx.render(p, a)
+        bs = ctx.upload(sc)
+        assert bs.reserved == 1 and bs.ms_total == 0.0 and bs.built_on_device == 1
+        b = np.zeros((h, w, 3), np.float32); ctx.render(p, b)
+        assert _bits_equal(a, b) and np.nansum(a) > 0
+        # camera only: another resolution -> inv_image_size differs, tables are the same
+        d = _ffi.SceneDesc.from_buffer_copy(sc.desc)
+        d.cam.pos[0] += 0.75
+        moved = Scene.from_desc(d, w, h, n)
+        assert ctx.upload(moved).reserved == 1
+        c_img = np.zeros((h, w, 3), np.float32); ctx.render(p, c_img)
+        assert not _bits_equal(a, c_img) and _bits_equal(c_img, fresh(moved))
+        # one surface moved: rebuilt
+        f = tmp_path / "changed.urn"
+        f.write_text(HEADER.format(w=w, h=h, n=n) + SCENES["sphere-light"].replace("sphere [-1.5 0.5 0] 1", "sphere [-1.25 0.5 0] 1"))
+        changed = Scene.load_urn(str(f))
+        assert ctx.upload(changed).reserved == 0
+        d_img = np.zeros((h, w, 3), np.float32); ctx.render(p, d_img)
+        assert not _bits_equal(a, d_img) and _bits_equal(d_img, fresh(changed))
+        # and back: rebuilt again (only the scene that IS on the device is remembered), same image as at first
+        assert ctx.upload(sc).reserved == 0
+        e = np.zeros((h, w, 3), np.float32); ctx.render(p, e)
+        assert _bits_equal(a, e)
+        # the host build is another build: not confused with the device build of the same tables
+        assert ctx.upload(sc, build="host").reserved == 0 and ctx.upload(sc, build="host").reserved == 1
+    finally:
+        ctx.close()
