@@ -38,6 +38,7 @@ COMMON = [
     *(["-DPLU_PREFETCH_FAR=" + os.environ["PLU_PREFETCH_FAR"]] if os.environ.get("PLU_PREFETCH_FAR") else []),
     *(["-DPLU_PT_BLOCKS=" + os.environ["PLU_PT_BLOCKS"]] if os.environ.get("PLU_PT_BLOCKS") else []),
     *(["-DPLU_SEED_AREA=" + os.environ["PLU_SEED_AREA"]] if os.environ.get("PLU_SEED_AREA") else []),
+    *(["-DPLU_SHADE_BLOCKS=" + os.environ["PLU_SHADE_BLOCKS"]] if os.environ.get("PLU_SHADE_BLOCKS") else []),
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread",
 ]
 

@@ -449,8 +449,11 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_PT_BLOCKS) k_extend_pt(const __gr
 // One path vertex: everything renderer.cpp:66-83 does between two scene->hit calls, except the
 // visibility tests of estimate_direct_light, which become shadow entries for k_connect.  One
 // instantiation per material class; the queue it reads holds only vertices of that class.
+#ifndef PLU_SHADE_BLOCKS
+#define PLU_SHADE_BLOCKS 3   // resident CTAs per SM k_shade is compiled for (3: 80 registers; 4: 64 registers and spills, a build option)
+#endif
 template <bool SMEM, int CLS>
-__global__ void __launch_bounds__(PLU_CTA, 3) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
+__global__ void __launch_bounds__(PLU_CTA, PLU_SHADE_BLOCKS) k_shade(const __grid_constant__ scene_ref sc_in, const __grid_constant__ wave_buffers wb, int bounce_arg) {
 	const int bounce = wave_vertex(wb, bounce_arg);
 	scene_ref sc = sc_in;
 	const wave_desc w = *wb.desc;
