@@ -340,9 +340,12 @@ def bench_config(name, args, rank, world, local, host_group):
     rays_per_sample = (st.rays_extend + st.rays_shadow) / max(st.samples, 1)
 
     # ---- e2e: the reference-facing call with HOST buffers ----------------------------------------------------------
-    tx = texture2d((W, H))
     fb_bytes = W * H * 3 * 4
     n_e2e = max(1, min(args.steps, 2))
+    # one zero-filled target per call, as main.cpp:175 makes a fresh texture2d per image (render accumulates, `+=`); the pixels are
+    # page-locked host memory (plu_host_alloc), which is what the e2e contract asks the host side of the copies to be
+    targets = [texture2d((W, H), pinned=True) for _ in range(n_e2e + 1)]
+    next_target = iter(targets)
     full = spp == NSTRATA * NSTRATA
     e2e_torchrun = None
 
@@ -373,7 +376,7 @@ def bench_config(name, args, rank, world, local, host_group):
         r = renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, seed=SEED)
 
         def e2e_step():   # scene upload + framebuffer H2D (`+=`) + render + framebuffer D2H, all inside plu_gpu_render
-            tx.pixels.fill(0)
+            tx = next(next_target)
             if full:
                 return r.render(tx)
             p = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=0, sample_stride=1, sample_count=spp)
@@ -390,8 +393,7 @@ def bench_config(name, args, rank, world, local, host_group):
         r = sharded_renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, rank=rank, world=world, seed=SEED)
 
         def e2e_step():   # rank 0: pinned host pixels -> device; all: render own strata; NCCL reduce; rank 0: device -> host
-            tx.pixels.fill(0)
-            return r.render(tx, spp=spp)
+            return r.render(next(next_target), spp=spp)
         dt = timed(e2e_step, True)
         r.ctx.close()
         e2e_torchrun = {"value": samples_per_step / dt / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": fb_bytes, "d2h_bytes_per_step": fb_bytes,
@@ -408,8 +410,12 @@ def bench_config(name, args, rank, world, local, host_group):
             p = GpuContext.params(W, H, NSTRATA, seed=SEED, sample_begin=0, sample_stride=1, sample_count=spp)
             ms_red = []
 
+            next_target = iter(targets)
+            for t in targets:
+                t.pixels.fill(0)
+
             def multi_step():
-                tx.pixels.fill(0)
+                tx = next(next_target)
                 m.upload(scene)
                 s = m.render(p, tx.pixels)
                 ms_red.append(s.ms_reduce)

@@ -16,6 +16,7 @@
 #ifndef PLUGPU_H
 #define PLUGPU_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -331,6 +332,20 @@ int plu_gpu_encode_bmp_device_noalloc(plu_gpu_ctx* ctx, int32_t width, int32_t h
  * :209 — use plu_gpu_encode_bmp for that flow).                                                 */
 int plu_gpu_postprocess_resident(plu_gpu_ctx* ctx, float* rgb_out);
 int plu_gpu_encode_bmp_resident(plu_gpu_ctx* ctx, uint32_t flags, unsigned char* out_bmp, int64_t cap);
+
+/* Page-locked host images.  texture2d::_pixels is `new vec3[w*h]` (texture.h:29,36): pageable
+ * memory, which the driver copies through its own staging buffer at a fraction of the PCIe rate —
+ * for an image that renders in a few milliseconds (glass0, refrac0, minimal0) the two copies of
+ * plu_gpu_render then cost as much as the render.  plu_host_alloc returns ZERO-FILLED memory
+ * (vec3() zero-initialises) that is pinned for every device of the box; plu_host_register pins
+ * memory the caller already owns (an existing texture2d's pixels) until plu_host_unregister,
+ * which must run before that memory is freed.  Any pointer into such memory may be handed to the
+ * entry points that take HOST images; nothing else changes (pageable pointers keep working).
+ * PLU_E_ARG for NULL / 0 bytes, PLU_E_CUDA when there is no device or the driver refuses.      */
+int plu_host_alloc(size_t bytes, void** out);
+int plu_host_free(void* p);
+int plu_host_register(void* p, size_t bytes);
+int plu_host_unregister(void* p);
 
 /* ---- host-side scene plumbing (no GPU needed) --------------------------------------------- */
 typedef struct plu_scene plu_scene;   /* owns the arrays a plu_scene_desc points at              */

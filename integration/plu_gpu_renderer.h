@@ -218,6 +218,20 @@ inline plu_gpu_ctx* shared_ctx() {
 	if (rc != PLU_OK) throw std::runtime_error(plu_gpu_last_error(nullptr));
 	return h.c;
 }
+
+// Page-locks the pixels of an existing texture2d (`new vec3[w*h]`, texture.h:29,36) for the guard's lifetime, so that the two
+// PCIe copies of gpu_renderer::render run at the link rate; worth it when the same target is rendered into more than once or
+// the render itself takes milliseconds.  An optimisation only: if the driver refuses, the target simply stays pageable.
+struct pinned_target {
+	void* p = nullptr;
+	explicit pinned_target(const shared_ptr<texture2d>& t) {
+		void* q = &t->pixel(uvec2(0, 0)).x;
+		if (plu_host_register(q, (size_t)t->size.x * t->size.y * sizeof(vec3)) == PLU_OK) p = q;
+	}
+	~pinned_target() { if (p) plu_host_unregister(p); }
+	pinned_target(const pinned_target&) = delete;
+	pinned_target& operator=(const pinned_target&) = delete;
+};
 }  // namespace gpu
 
 // Same constructor and render() signature as plu::renderer (renderer.h:20-25).

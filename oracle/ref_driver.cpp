@@ -256,12 +256,15 @@ int main(int argc, char** argv) {
 			                    flat ? F.lights : L.sc->lights);
 			// PLU_REF_REPEAT=k: render k times into fresh targets (the context, wave buffers and NCCL communicators of
 			// the drop-in live across calls), report the LAST call's time; PLU_REF_FUSED=1 (with a .bmp argument): the
-			// resident-framebuffer flow gpu_render_post_write, <out.bin> then holds the tone-mapped image
+			// resident-framebuffer flow gpu_render_post_write, <out.bin> then holds the tone-mapped image; PLU_REF_PIN=1: the
+			// target's pixels are page-locked first (plu::gpu::pinned_target, outside the timed call)
 			const int repeat = std::getenv("PLU_REF_REPEAT") ? std::max(1, atoi(std::getenv("PLU_REF_REPEAT"))) : 1;
 			const bool fused = argc == 8 && std::getenv("PLU_REF_FUSED") != nullptr;
 			double ms = 0.0, ms_first = 0.0;
 			for (int it = 0; it < repeat; ++it) {
 				if (it > 0) tx = std::make_shared<plu::texture2d>(glm::uvec2(w, h));
+				std::unique_ptr<plu::gpu::pinned_target> pin;
+				if (std::getenv("PLU_REF_PIN")) pin.reset(new plu::gpu::pinned_target(tx));
 				auto t0 = std::chrono::high_resolution_clock::now();
 				if (fused) plu::gpu_render_post_write(r, tx, argv[7]); else r.render(tx);
 				auto t1 = std::chrono::high_resolution_clock::now();

@@ -5,6 +5,7 @@ import os
 from ._build import LIB_PATH  # noqa: F401
 
 PLU_OK = 0
+PLU_E_ARG, PLU_E_CUDA, PLU_E_NOSCENE, PLU_E_IO, PLU_E_PARSE, PLU_E_NOMEM = -1, -2, -3, -4, -5, -6
 ERRORS = {-1: "PLU_E_ARG", -2: "PLU_E_CUDA", -3: "PLU_E_NOSCENE", -4: "PLU_E_IO", -5: "PLU_E_PARSE", -6: "PLU_E_NOMEM"}
 
 PRIM_SPHERE, PRIM_BOX, PRIM_TRIANGLE = 0, 1, 2
@@ -102,6 +103,10 @@ SYMBOLS = {
     "plu_gpu_encode_bmp_device_noalloc": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_uint32, _P, _P, C.c_int64]),
     "plu_gpu_postprocess_resident": (C.c_int, [_P, _P]),
     "plu_gpu_encode_bmp_resident": (C.c_int, [_P, C.c_uint32, _P, C.c_int64]),
+    "plu_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "plu_host_free": (C.c_int, [_P]),
+    "plu_host_register": (C.c_int, [_P, C.c_size_t]),
+    "plu_host_unregister": (C.c_int, [_P]),
     "plu_scene_load_urn": (C.c_int, [C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_load_flat": (C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_int]),
     "plu_scene_save_flat": (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, C.c_int32, C.c_char_p]),

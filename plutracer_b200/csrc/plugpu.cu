@@ -1297,3 +1297,32 @@ extern "C" int plu_scene_reference_leaf_order(const plu_scene_desc* desc, int32_
 	std::copy(r.begin(), r.end(), rank);
 	return PLU_OK;
 }
+
+// ---- page-locked host images (plugpu.h: plu_host_*) ---------------------------------------------------------------
+// No context: the memory is pinned for every device (cudaHostAllocPortable / cudaHostRegisterPortable), so the same image can
+// be handed to a single- or a multi-device context.  cudaGetLastError() clears the sticky error a refused call leaves.
+extern "C" int plu_host_alloc(size_t bytes, void** out) {
+	if (!out) return PLU_E_ARG;
+	*out = nullptr;
+	if (bytes == 0) return PLU_E_ARG;
+	void* p = nullptr;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return PLU_E_CUDA; }
+	std::memset(p, 0, bytes);
+	*out = p;
+	return PLU_OK;
+}
+extern "C" int plu_host_free(void* p) {
+	if (!p) return PLU_OK;
+	if (cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return PLU_E_CUDA; }
+	return PLU_OK;
+}
+extern "C" int plu_host_register(void* p, size_t bytes) {
+	if (!p || bytes == 0) return PLU_E_ARG;
+	if (cudaHostRegister(p, bytes, cudaHostRegisterPortable) != cudaSuccess) { cudaGetLastError(); return PLU_E_CUDA; }
+	return PLU_OK;
+}
+extern "C" int plu_host_unregister(void* p) {
+	if (!p) return PLU_E_ARG;
+	if (cudaHostUnregister(p) != cudaSuccess) { cudaGetLastError(); return PLU_E_CUDA; }
+	return PLU_OK;
+}

@@ -120,12 +120,40 @@ class stratified_sampler:
             raise ValueError("the reference always passes uvec2(sc.samples): sample_count.x == sample_count.y")
 
 
-class texture2d:
-    """texture2d as a render target (texture.h:26-47): float RGB, row-major, y down, size = (W, H)."""
+def pinned_zeros(shape, dtype=np.float32):
+    """A zero-filled numpy array in page-locked host memory (plu_host_alloc), freed with the array.  Raises PluError
+    when there is no CUDA device."""
+    import weakref
+    lib = _ffi.lib()
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    rc = lib.plu_host_alloc(n, C.byref(p))
+    if rc != _ffi.PLU_OK:
+        raise _ffi.PluError(rc, "plu_host_alloc: no page-locked host memory (no CUDA device?)")
+    buf = (C.c_char * n).from_address(p.value)
+    a = np.frombuffer(buf, dtype=dtype).reshape(shape)
+    weakref.finalize(buf, lib.plu_host_free, C.c_void_p(p.value))   # `a` keeps `buf` alive through its .base chain
+    return a
 
-    def __init__(self, size):
+
+class texture2d:
+    """texture2d as a render target (texture.h:26-47): float RGB, row-major, y down, size = (W, H).
+    pinned=True puts the pixels in page-locked memory (plu_host_alloc): the two PCIe copies of renderer.render then run
+    at the link rate instead of through the driver's staging buffer; pinned=None does so when a device is present."""
+
+    def __init__(self, size, pinned=False):
         self.size = (int(size[0]), int(size[1]))
-        self.pixels = np.zeros((self.size[1], self.size[0], 3), np.float32)   # GLM vec3() zero-inits
+        shape = (self.size[1], self.size[0], 3)
+        self.pinned = False
+        if pinned or pinned is None:
+            try:
+                self.pixels = pinned_zeros(shape)
+                self.pinned = True
+            except (_ffi.PluError, RuntimeError):
+                if pinned:
+                    raise
+        if not self.pinned:
+            self.pixels = np.zeros(shape, np.float32)   # GLM vec3() zero-inits
 
     def pixel(self, c):
         return self.pixels[c[1], c[0]]

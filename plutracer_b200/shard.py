@@ -64,9 +64,14 @@ class sharded_renderer:
             self._fb = torch.empty(H, W, 3, dtype=torch.float32, device=dev)
             self._host = torch.empty(H, W, 3, dtype=torch.float32).pin_memory()
         stream = torch.cuda.current_stream(dev)
+        # a page-locked target (texture2d(pinned=True)) is copied from and to directly; a pageable one goes through self._host
+        direct = torch.from_numpy(target.pixels.reshape(H, W, 3)) if getattr(target, "pinned", False) else None
         if self.rank == 0:   # the caller's pixels enter the sum once
-            self._host.copy_(torch.from_numpy(target.pixels.reshape(H, W, 3)))
-            self._fb.copy_(self._host, non_blocking=True)
+            if direct is not None:
+                self._fb.copy_(direct, non_blocking=True)
+            else:
+                self._host.copy_(torch.from_numpy(target.pixels.reshape(H, W, 3)))
+                self._fb.copy_(self._host, non_blocking=True)
         else:
             self._fb.zero_()
         if count > 0:
@@ -74,9 +79,10 @@ class sharded_renderer:
             self.last_stats = self.ctx.render_device(p, self._fb.data_ptr(), stream.cuda_stream)
         reduce_framebuffer(self._fb, dst=0)
         if self.rank == 0:
-            self._host.copy_(self._fb, non_blocking=True)
+            (direct if direct is not None else self._host).copy_(self._fb, non_blocking=True)
             stream.synchronize()
-            target.pixels.reshape(H, W, 3)[...] = self._host.numpy()
+            if direct is None:
+                target.pixels.reshape(H, W, 3)[...] = self._host.numpy()
         return self.last_stats
 
     def close(self):

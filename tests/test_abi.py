@@ -66,3 +66,21 @@ def test_bad_inputs_rejected(lib, tmp_path):
     d = _ffi.SceneDesc()
     d.abi_version = 99
     assert lib.plu_scene_save_flat(C.byref(d), 1, 1, 1, b"/tmp/x") == -1
+
+
+def test_host_memory_entry_points_reject_bad_arguments(lib):
+    """plu_host_*: argument errors need no device; without one the allocation itself is refused (no pageable stand-in)."""
+    import torch
+    from plutracer_b200 import _ffi
+    p = C.c_void_p()
+    assert lib.plu_host_alloc(0, C.byref(p)) == _ffi.PLU_E_ARG and not p.value
+    assert lib.plu_host_alloc(64, None) == _ffi.PLU_E_ARG
+    assert lib.plu_host_register(None, 64) == _ffi.PLU_E_ARG
+    assert lib.plu_host_unregister(None) == _ffi.PLU_E_ARG
+    assert lib.plu_host_free(None) == _ffi.PLU_OK
+    if not torch.cuda.is_available():
+        assert lib.plu_host_alloc(64, C.byref(p)) == _ffi.PLU_E_CUDA and not p.value
+        from plutracer_b200 import texture2d
+        with pytest.raises(_ffi.PluError):
+            texture2d((4, 4), pinned=True)
+        assert not texture2d((4, 4), pinned=None).pinned

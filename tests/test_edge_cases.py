@@ -141,3 +141,34 @@ def test_upload_of_an_unchanged_scene_keeps_the_device_tables(lib, tmp_path):
         assert ctx.upload(sc, build="host").reserved == 0 and ctx.upload(sc, build="host").reserved == 1
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_page_locked_targets_change_nothing_but_the_copy_rate(gpu, lib):
+    """plu_host_alloc / plu_host_register: a render into a page-locked target (texture2d(pinned=True)), into a registered
+    numpy array and into pageable memory gives the same bits, incl. a NON-ZERO target (`+=`); the allocation is zero-filled."""
+    import ctypes as C
+    from plutracer_b200 import GpuContext, _ffi, renderer, sharded_renderer, stratified_sampler, texture2d
+    from tests.orc import golden_scene
+    w, h, n = 80, 56, 3
+    sc = golden_scene("room", w, h, n)
+    r = renderer(sc, None, (32, 32), stratified_sampler((w, h), (n, n)), None)
+    a, b = texture2d((w, h)), texture2d((w, h), pinned=True)
+    assert b.pinned and not a.pinned and not b.pixels.any()
+    a.pixels[...] = 0.25; b.pixels[...] = 0.25
+    r.render(a); r.render(b)
+    assert _bits_equal(a.pixels, b.pixels) and np.nansum(a.pixels) > 0.25 * a.pixels.size
+    c = np.full((h, w, 3), 0.25, np.float32)
+    assert lib.plu_host_register(c.ctypes.data, c.nbytes) == _ffi.PLU_OK
+    try:
+        r.ctx.render(GpuContext.params(w, h, n, seed=r.seed), c)
+    finally:
+        assert lib.plu_host_unregister(c.ctypes.data) == _ffi.PLU_OK
+    assert _bits_equal(a.pixels, c)
+    assert lib.plu_host_unregister(c.ctypes.data) == _ffi.PLU_E_CUDA   # not registered any more: refused, and no sticky error is left
+    r.render(texture2d((w, h)))
+    s = sharded_renderer(sc, None, (32, 32), stratified_sampler((w, h), (n, n)), None, rank=0, world=1)
+    d = texture2d((w, h), pinned=True); d.pixels[...] = 0.25
+    s.render(d)
+    assert _bits_equal(a.pixels, d.pixels)
+    r.ctx.close(); s.close()

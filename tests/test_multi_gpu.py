@@ -199,6 +199,10 @@ def test_dropin_resident_framebuffer_flow(lib, tmp_path):
     _dropin(["render-gpu-flat", scene, w, h, n, a_img, a_bmp], {"PLU_DEVICES": "0"})
     _dropin(["render-gpu-flat", scene, w, h, n, b_img, b_bmp], {"PLU_DEVICES": "0", "PLU_REF_FUSED": "1"})
     assert open(a_bmp, "rb").read() == open(b_bmp, "rb").read()
+    # plu::gpu::pinned_target around the reference's own texture2d (plu_host_register): same bytes
+    c_img, c_bmp = str(tmp_path / "c.bin"), str(tmp_path / "c.bmp")
+    _dropin(["render-gpu-flat", scene, w, h, n, c_img, c_bmp], {"PLU_DEVICES": "0", "PLU_REF_PIN": "1", "PLU_REF_REPEAT": "2"})
+    assert open(a_bmp, "rb").read() == open(c_bmp, "rb").read() and open(a_img, "rb").read() == open(c_img, "rb").read()
     from plutracer_b200 import GpuContext
     lin = np.fromfile(a_img, np.float32).reshape(h, w, 3)
     ctx = GpuContext(0)
