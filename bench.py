@@ -387,7 +387,8 @@ def bench_config(name, args, rank, world, local, host_group):
         e2e = {"value": samples_per_step / dt / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": fb_bytes, "d2h_bytes_per_step": fb_bytes,
                "ms_per_step": dt * 1e3, "first_call_ms": first_call["ms"],
                "timing": "host wall clock around renderer(...).render(target): plu_gpu_upload_scene (the scene is unchanged between steps: its tables are "
-                         "compared with those on the device and kept; first_call_ms is the call that copied and built them) + framebuffer H2D + render + D2H",
+                         "compared with those on the device and kept; first_call_ms is the call that copied and built them) + framebuffer H2D + render + D2H; "
+                         "the target is a fresh zero texture2d per call in page-locked host memory (plu_host_alloc)",
                "path": "C ABI, one device"}
     else:
         r = sharded_renderer(scene, None, (32, 32), stratified_sampler((W, H), (NSTRATA, NSTRATA)), None, device=local, rank=rank, world=world, seed=SEED)
