@@ -94,6 +94,21 @@ PLU_DEV float det_cos(float x) {
 	float y = (j == 1 || j == 2) ? trig_poly_sin(r) : trig_poly_cos(r);
 	return sign * y;
 }
+// det_cos(x) and det_sin(x) of the same angle with ONE reduction and one evaluation of each polynomial (the two calls side by
+// side evaluate them up to four times: the compiler does not merge the selects).  Same operations on the same values, so the
+// results are det_cos / det_sin bit for bit.
+PLU_DEV void det_sincos(float x, float& s_out, float& c_out) {
+	if (!(fabsf(x) <= 8192.f)) { s_out = c_out = x - x; return; }
+	float sign_s = 1.f, sign_c = 1.f, ax = x;
+	if (x < 0.f) { sign_s = -1.f; ax = -x; }
+	float r; int j = trig_reduce(ax, r) & 7;
+	if (j > 3) { sign_s = -sign_s; sign_c = -sign_c; j -= 4; }
+	if (j > 1) sign_c = -sign_c;
+	const float ps = trig_poly_sin(r), pc = trig_poly_cos(r);
+	const bool swap = (j == 1 || j == 2);
+	s_out = sign_s * (swap ? pc : ps);
+	c_out = sign_c * (swap ? ps : pc);
+}
 PLU_DEV float det_asin(float x) {
 	float a = x < 0.f ? -x : x;
 	if (!(a <= 1.f)) return (x - x) / (x - x);

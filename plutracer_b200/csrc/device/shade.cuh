@@ -37,24 +37,29 @@ struct vertex_rng {
 
 // ---- sampling warps, cmmn.h:257-298 --------------------------------------------------------------------
 PLU_DEV f2 concentric_disk_sample(f2 u) {
-	f2 rt;
 	u = mk2(2.f * u.x - 1.f, 2.f * u.y - 1.f);
 	if (u.x == 0.f && u.y == 0.f) return mk2(0.f, 0.f);
-	if (u.x >= -u.y) {
-		if (u.x > u.y) rt = mk2(u.x, u.y > 0.f ? u.y / u.x : 8.f + u.y / u.x);
-		else rt = mk2(u.y, 2.f - u.x / u.y);
-	} else {
-		if (u.x <= u.y) rt = mk2(-u.x, 4.f - u.y / u.x);
-		else rt = mk2(-u.y, 6.f - u.x / u.y);
-	}
+	// cmmn.h:262-279 has one division per quadrant of the square (u.y / u.x or u.x / u.y, then q, 8 + q, 2 - q, 4 - q or 6 - q).  The
+	// lanes of a warp fall into all four, so the quadrant only SELECTS the operands here and the division is issued once: the same
+	// operands meet the same operations, the result is the reference's bit for bit.
+	const bool A = u.x >= -u.y;
+	const bool B = A ? (u.x > u.y) : (u.x <= u.y);   // B: u.y / u.x, radius +-u.x; else u.x / u.y, radius +-u.y
+	const float num = B ? u.y : u.x, den = B ? u.x : u.y;
+	const float q = num / den;
+	f2 rt;
+	rt.x = A ? den : -den;
+	if (A && B) rt.y = u.y > 0.f ? q : 8.f + q;
+	else rt.y = (A ? 2.f : (B ? 4.f : 6.f)) - q;
 	rt.y *= PLU_PI * .25f;
-	return mk2(det_cos(rt.y) * rt.x, det_sin(rt.y) * rt.x);
+	float sn, cs; det_sincos(rt.y, sn, cs);
+	return mk2(cs * rt.x, sn * rt.x);
 }
 PLU_DEV f3 uniform_sphere_sample(f2 u) {
 	float z = 1.f - 2.f * u.x;
 	float r = sqrtf(gmax(0.f, 1.f - z * z));
 	float phi = 2.f * PLU_PI * u.y;
-	return mk3(r * det_cos(phi), r * det_sin(phi), z);
+	float sn, cs; det_sincos(phi, sn, cs);
+	return mk3(r * cs, r * sn, z);
 }
 PLU_DEV f3 cosine_hemisphere_sample(f2 u) {
 	f2 d = concentric_disk_sample(u);
@@ -240,7 +245,9 @@ struct bsdf {
 	}
 };
 
-PLU_DEV void make_bsdf(const scene_ref& sc, const plu_material_desc& m, const hit_rec& hr, bsdf& b) {
+// unit_dpdu: the caller knows that hr.dpdu is an axis unit vector (box::hit, box.cpp:31-36): normalize() of it multiplies by
+// 1 / sqrt(1) = 1 and is skipped
+PLU_DEV void make_bsdf(const scene_ref& sc, const plu_material_desc& m, const hit_rec& hr, bsdf& b, bool unit_dpdu = false) {
 	b.tag = m.tag;
 	b.R = (m.texture >= 0) ? texel(sc, sc.texture(m.texture), hr.uv) : mk3(m.color[0], m.color[1], m.color[2]);
 	b.eta = mk3(m.p0[0], m.p0[1], m.p0[2]); b.k = mk3(m.p1[0], m.p1[1], m.p1[2]);
@@ -248,7 +255,7 @@ PLU_DEV void make_bsdf(const scene_ref& sc, const plu_material_desc& m, const hi
 	// perfect-refraction(color, eta_t, eta_i) -> Fr.eta_i = eta_t, Fr.eta_t = eta_i; glass -> (1, ior)
 	if (m.tag == PLU_MAT_PERFECT_REFRACTION) { b.fr_eta_i = m.p0[0]; b.fr_eta_t = m.p0[1]; }
 	else { b.fr_eta_i = 1.f; b.fr_eta_t = m.p0[0]; }
-	b.N = hr.norm; b.S = normalize(hr.dpdu); b.T = cross(b.N, b.S);
+	b.N = hr.norm; b.S = unit_dpdu ? hr.dpdu : normalize(hr.dpdu); b.T = cross(b.N, b.S);
 }
 
 // ---- area-light surfaces: surface::sample / surface::pdf ---------------------------------------------------

@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_SHADE_BLOCKS) k_shade(const __gri
 				L = L + T * mk3(0.f);
 				wb.rad[slot] = make_float4(L.x, L.y, L.z, 0.f);
 			}
-			make_bsdf(sc, m, hr, b);
+			make_bsdf(sc, m, hr, b, meta.x == PLU_PRIM_BOX);
 			if (CLS == CLS_DIFFUSE) b.tag = PLU_MAT_DIFFUSE;   // compile-time constant for everything below
 			// renderer.cpp:53-57 + :5-51 up to the visibility tests
 			if (CLS == CLS_DIFFUSE && sc.n_lights > 0) {

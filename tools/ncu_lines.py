@@ -12,7 +12,13 @@ import tempfile
 
 
 def sass_rows(rep, which):
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
+    """rep: an .ncu-rep, or the gzipped `--page source --csv --print-source sass` export tools/ncu_capture.sh leaves; which: block
+    index, or a kernel-name substring (then the launch of that kernel with the most samples)"""
+    if rep.endswith(".gz"):
+        import gzip
+        out = gzip.open(rep, "rt").read()
+    else:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
     blocks, cur = [], None
     for row in csv.reader(out.splitlines()):
         if row and row[0] == "Kernel Name":
@@ -22,6 +28,9 @@ def sass_rows(rep, which):
         if cur["hdr"] is None:
             cur["hdr"] = row; continue
         cur["rows"].append(row)
+    if isinstance(which, str):
+        cand = [b for b in blocks if which in b["name"]]
+        return max(cand, key=lambda b: sum(int(r[b["hdr"].index("# Samples")] or 0) for r in b["rows"]))
     return blocks[which]
 
 
@@ -72,4 +81,5 @@ def main(rep, so, kernel, which=0, top=40, outer=False):
 
 if __name__ == "__main__":
     a = [x for x in sys.argv if x != "--outer"]   # --outer: attribute inlined code to the outermost call site
-    main(a[1], a[2], a[3], int(a[4]) if len(a) > 4 else 0, int(a[5]) if len(a) > 5 else 40, "--outer" in sys.argv)
+    which = (int(a[4]) if a[4].lstrip("-").isdigit() else a[4]) if len(a) > 4 else 0
+    main(a[1], a[2], a[3], which, int(a[5]) if len(a) > 5 else 40, "--outer" in sys.argv)
