@@ -63,6 +63,18 @@ PLU_DEV void slabs_fast(f3 mn, f3 mx, f3 e, f3 rrd, float& tmin, float& tmax) {
 	tmax = fmin3_nan(fmax_nan(t1.x, t2.x), fmax_nan(t1.y, t2.y), fmax_nan(t1.z, t2.z));
 }
 
+// Packed fp32 pairs (sm_100 FADD2 / FMUL2: two IEEE round-to-nearest results per issue slot): the plane
+// distances of BOTH children of a fast node along one axis side are one subtract + one multiply.
+PLU_DEV unsigned long long pk2(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+PLU_DEV void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+PLU_DEV unsigned long long submul2(unsigned long long m, unsigned long long e, unsigned long long i) {
+	unsigned long long t;
+	asm("{\n\t.reg .b64 d;\n\tsub.rn.f32x2 d, %1, %2;\n\tmul.rn.f32x2 %0, d, %3;\n\t}" : "=l"(t) : "l"(m), "l"(e), "l"(i));
+	return t;
+}
+PLU_DEV float fmin3f(float a, float b, float c) { float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+
 // t-only versions of surface::hit(r, hr) with hr->t == bound on entry.
 PLU_DEV bool sphere_t(float4 cr, const ray& r, float bound, float& t) {   // sphere.cpp:17-26
 	f3 v = r.e - mk3(cr);
@@ -221,6 +233,9 @@ PLU_DEV bool trace_ref(const scene_ref& sc, const ray& r, float root_bound, floa
 // leaves (a box leaf's node bounds ARE the box, bvh_build.cpp) share one branch-free slab test; a
 // sphere leaf carries (centre, radius) in its node; only triangles fetch primitive data.  Tested
 // surfaces and the tie rule are unchanged.
+// SMEM: the staged nodes are in the paired layout stage_scene(.., pair_nodes = true) leaves — a = (min.x max.x min.y max.y),
+// b = (min.z max.z aux prim) — and the six plane distances are three packed fp32x2 subtract + multiply pairs (sub.rn / mul.rn per
+// half: the scalar results bit for bit, in half the issue slots).
 template <bool COUNT, bool SMEM>
 PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bound, float& t_out, int32_t& prim_out, trace_counts* tc) {
 	const ref_node* nodes = sc.ref_nodes();
@@ -230,15 +245,34 @@ PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bou
 	const float bound = n == 1 ? root_bound : PLU_T_MAX;
 	float best_t = 0.f; int32_t best = -1;
 	int32_t skip_to = 0;
+	unsigned long long ex2 = 0, ey2 = 0, ez2 = 0, ix2 = 0, iy2 = 0, iz2 = 0;
+	if (SMEM) {
+		ex2 = pk2(r.e.x, r.e.x); ey2 = pk2(r.e.y, r.e.y); ez2 = pk2(r.e.z, r.e.z);
+		ix2 = pk2(rrd.x, rrd.x); iy2 = pk2(rrd.y, rrd.y); iz2 = pk2(rrd.z, rrd.z);
+	}
 #pragma unroll 2
 	for (int32_t i = 0; i < n; ++i) {
-		float4 lo = nodes[i].lo, hi = nodes[i].hi;
+		float4 lo, hi;
+		if (SMEM) {
+			const float4 a = nodes[i].lo, b = nodes[i].hi;
+			lo = make_float4(a.x, a.z, b.x, b.z); hi = make_float4(a.y, a.w, b.y, b.w);   // (only what is used below stays live)
+		} else { lo = nodes[i].lo; hi = nodes[i].hi; }
 		const int32_t prim = __float_as_int(hi.w), aux = __float_as_int(lo.w);   // aux: skip index | surface kind
 		const bool live = i >= skip_to;
 		const bool interior = prim < 0;
 		if (interior || aux == PLU_PRIM_BOX) {
-			float tmin, tmax; slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
-			if ((tmin != tmin) || (!interior && tmin == 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);   // hazard: exact glm order
+			float tmin, tmax;
+			if (SMEM) {
+				float ax, bx, ay, by, az, bz;   // (min - e) * rrd, (max - e) * rrd per axis
+				upk2(submul2(pk2(lo.x, hi.x), ex2, ix2), ax, bx);
+				upk2(submul2(pk2(lo.y, hi.y), ey2, iy2), ay, by);
+				upk2(submul2(pk2(lo.z, hi.z), ez2, iz2), az, bz);
+				tmin = fmax3_nan(fmin_nan(ax, bx), fmin_nan(ay, by), fmin_nan(az, bz));
+				tmax = fmin3_nan(fmax_nan(ax, bx), fmax_nan(ay, by), fmax_nan(az, bz));
+			} else slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
+			// hazard (NaN plane distance; a box hit at distance 0): exact glm order.  One compare: `!(|tmin| > 0)` is NaN or zero — an
+			// interior node with tmin == 0 takes the exact path too, which changes nothing but the route
+			if (!(fabsf(tmin) > 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
 			if (interior) {
 				if (COUNT && live) tc->nodes++;
 				if (live && !(tmax >= tmin)) skip_to = aux;
@@ -269,18 +303,6 @@ PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bou
 // d == 0 on that axis) drop out of fminf/fmaxf, i.e. count as "inside".  What it does NOT reproduce is
 // the reference losing a true hit because one of its own origin-inflated ancestor boxes rejects the
 // ray by rounding; tests compare both walks on every named scene and on the synthetic ones.
-// Packed fp32 pairs (sm_100 FADD2 / FMUL2: two IEEE round-to-nearest results per issue slot): the plane
-// distances of BOTH children of a fast node along one axis side are one subtract + one multiply.
-PLU_DEV unsigned long long pk2(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-PLU_DEV void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-PLU_DEV unsigned long long submul2(unsigned long long m, unsigned long long e, unsigned long long i) {
-	unsigned long long t;
-	asm("{\n\t.reg .b64 d;\n\tsub.rn.f32x2 d, %1, %2;\n\tmul.rn.f32x2 %0, d, %3;\n\t}" : "=l"(t) : "l"(m), "l"(e), "l"(i));
-	return t;
-}
-PLU_DEV float fmin3f(float a, float b, float c) { float r; asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
-PLU_DEV float fmax3f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
-
 // Traversal stack of the fast walk: the lowest S levels live in shared memory (column threadIdx.x of an
 // [S][256] array: lanes at different depths still hit 32 different banks), deeper levels in the caller's local
 // array.  A local-only stack (S = 0) sends every push/pop through L1, where it competes with the node loads.

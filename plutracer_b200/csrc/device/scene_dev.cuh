@@ -68,13 +68,26 @@ struct scene_ref {
 #define PLU_SMEM_BLOB_MAX 16384
 
 // Stage the blob (call from all threads of the CTA; contains __syncthreads()).
-PLU_DEV void stage_scene(scene_ref& sc, unsigned char* smem) {
+// pair_nodes: the staged copy of the reference-tree nodes is rewritten in place from (min.xyz, skip | max.xyz, prim) to
+// (min.x max.x min.y max.y | min.z max.z skip prim), so that the uniform walk (isect.cuh: trace_ref_uniform<.., SMEM>) gets
+// the two planes of an axis as one 64-bit register pair for the packed fp32x2 subtract / multiply.  Only the CTA's own
+// shared-memory copy changes; the table in global memory (plu_gpu_download_table) keeps the layout above.
+PLU_DEV void stage_scene(scene_ref& sc, unsigned char* smem, bool pair_nodes = false) {
 	const uint4* src = (const uint4*)sc.blob;
 	uint4* dst = (uint4*)smem;
 	uint32_t n = sc.blob_bytes >> 4;
 	for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldg(src + i);
 	__syncthreads();
 	sc.blob = smem;
+	if (pair_nodes) {
+		float4* nd = (float4*)(smem + sc.off_ref_nodes);
+		for (uint32_t i = threadIdx.x; i < (uint32_t)sc.n_ref_nodes; i += blockDim.x) {
+			float4 lo = nd[2 * i], hi = nd[2 * i + 1];
+			nd[2 * i] = make_float4(lo.x, hi.x, lo.y, hi.y);
+			nd[2 * i + 1] = make_float4(lo.z, hi.z, lo.w, hi.w);
+		}
+		__syncthreads();
+	}
 }
 
 }  // namespace plud

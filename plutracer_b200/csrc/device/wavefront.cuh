@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 	if (PRIMARY) w = *wb.desc;
 	const uint32_t n = bounce == 0 ? wb.desc->n_slots : wb.counters[bounce * CNT_STRIDE + CNT_EXTEND];
 	if (blockIdx.x * PLU_CTA >= n) return;   // a CTA without a first entry has no work: leave before staging the scene
-	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
+	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem, sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st_o = (float4*)stage_base;            // [2][PLU_CTA]
 	float4* st_d = st_o + 2 * PLU_CTA;             // [2][PLU_CTA]
 	const uint32_t* q = wb.queue[bounce & 1];
@@ -671,7 +671,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_connect(const __grid_constant__ 
 	unsigned char* stage_base = (unsigned char*)plu_smem;
 	const uint32_t n = wb.counters[bounce * CNT_STRIDE + CNT_SHADOW];
 	if (blockIdx.x * PLU_CTA >= n) return;   // no work for this CTA: leave before staging the scene
-	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem); stage_base += (sc.blob_bytes + 127u) & ~127u; }
+	if (SMEM) { stage_scene(sc, (unsigned char*)plu_smem, sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES); stage_base += (sc.blob_bytes + 127u) & ~127u; }
 	float4* st = (float4*)stage_base;   // [2][3][PLU_CTA]: p, w1, c1 (the rare BSDF-sampled MIS ray's w2, c2 are fetched on demand)
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(wb.stats + 5, (unsigned long long)n);
 	const float nl = (float)sc.n_lights;
@@ -906,7 +906,7 @@ template <bool SMEM, bool COUNT = false>
 __global__ void __launch_bounds__(256) k_trace_rays(const __grid_constant__ scene_ref sc_in, int64_t n, const float* o3, const float* d3,
                                                     int primary_w, int primary_h, int32_t* id, float* t_out, float* n3) {
 	scene_ref sc = sc_in;
-	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem);
+	if (SMEM) stage_scene(sc, (unsigned char*)plu_smem, sc.n_ref_nodes <= PLU_UNIFORM_WALK_MAX_NODES);
 	for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
 		ray r;
 		if (primary_w > 0) {   // pixel-centre pinhole rays
