@@ -269,10 +269,16 @@ PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bou
 				upk2(submul2(pk2(lo.z, hi.z), ez2, iz2), az, bz);
 				tmin = fmax3_nan(fmin_nan(ax, bx), fmin_nan(ay, by), fmin_nan(az, bz));
 				tmax = fmin3_nan(fmax_nan(ax, bx), fmax_nan(ay, by), fmax_nan(az, bz));
-			} else slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
-			// hazard (NaN plane distance; a box hit at distance 0): exact glm order.  One compare: `!(|tmin| > 0)` is NaN or zero — an
-			// interior node with tmin == 0 takes the exact path too, which changes nothing but the route
-			if (!(fabsf(tmin) > 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
+				// hazard (a NaN plane distance; a box hit at distance 0, whose sign is returned): glm's select order on the SAME six
+				// plane distances.  A ray that leaves a box starts on one of its planes, so this is taken about once per secondary ray
+				if ((tmin != tmin) || (!interior && tmin == 0.f)) {
+					tmin = gmax(gmax(gmin(ax, bx), gmin(ay, by)), gmin(az, bz));
+					tmax = gmin(gmin(gmax(ax, bx), gmax(ay, by)), gmax(az, bz));
+				}
+			} else {
+				slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
+				if ((tmin != tmin) || (!interior && tmin == 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);   // hazard: exact glm order
+			}
 			if (interior) {
 				if (COUNT && live) tc->nodes++;
 				if (live && !(tmax >= tmin)) skip_to = aux;

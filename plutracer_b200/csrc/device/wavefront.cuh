@@ -20,6 +20,12 @@
 
 namespace plud {
 
+// Exact division of a numerator below 2^31 by a wave-uniform divisor: q = umulhi(n, m) >> sh with m = floor(2^(31 + l) / d) + 1,
+// l = ceil(log2 d), sh = l - 1 (the error m * d - 2^(31 + l) is at most d <= 2^l, so n * error < 2^(31 + l) for every n < 2^31);
+// d == 1 is passed through.  Five instructions where the generic 32-bit division takes ~20; set by the host (plugpu.cu: set_div).
+struct udiv32 { uint32_t d, m, sh; };
+PLU_DEV uint32_t div_by(uint32_t n, const udiv32& v) { return v.d == 1u ? n : (__umulhi(n, v.m) >> v.sh); }
+
 struct wave_desc {
 	int32_t width, height;      // target->size
 	int32_t n_strata;           // sample_count.x
@@ -31,6 +37,7 @@ struct wave_desc {
 	uint32_t n_slots;           // npix * kcount
 	int32_t use_lens;
 	int32_t use_dirty;          // 1: the wave started with k_primary — rad[slot] is only valid where the slot's dirty bit is set
+	udiv32 div_npix, div_width, div_strata;   // divisions by npix, width, n_strata
 };
 
 struct wave_buffers {
@@ -85,11 +92,11 @@ struct wave_buffers {
 
 
 PLU_DEV void slot_to_path(const wave_desc& w, uint32_t slot, philox_key& key, int32_t& px, int32_t& py, int32_t& s) {
-	uint32_t q = slot % (uint32_t)w.npix, k = slot / (uint32_t)w.npix;
+	const uint32_t k = div_by(slot, w.div_npix), q = slot - k * (uint32_t)w.npix;
 	int32_t pix = w.pix0 + (int32_t)q;
 	s = w.sample_begin + (w.k0 + (int32_t)k) * w.sample_stride;
 	int32_t wh = w.width * w.height;
-	if (pix >= wh) { px = w.width; py = pix - wh; } else { px = pix % w.width; py = pix / w.width; }
+	if (pix >= wh) { px = w.width; py = pix - wh; } else { py = (int32_t)div_by((uint32_t)pix, w.div_width); px = pix - py * w.width; }
 	key.pixel = (uint32_t)pix; key.sample = (uint32_t)s; key.k0 = w.seed_lo; key.k1 = w.seed_hi;
 }
 
@@ -205,7 +212,8 @@ PLU_DEV ray primary_ray(const scene_ref& sc, const wave_desc& w, uint32_t slot) 
 	u4 o = philox_call(key, 0u);
 	int32_t n = w.n_strata;
 	float dp = 1.f / (float)(uint32_t)n;
-	float sx = (float)(s % n), sy = (float)(s / n);
+	const int32_t sq = (int32_t)div_by((uint32_t)s, w.div_strata);
+	float sx = (float)(s - sq * n), sy = (float)sq;
 	f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);
 	f2 lens = mk2((sx + u01(o.z) * 0.999f) * dp, (sy + u01(o.w) * 0.999f) * dp);
 	return generate_ray(sc.cam, px, lens, w.use_lens != 0);

@@ -830,9 +830,22 @@ static int check_params(plu_gpu_ctx* ctx, const plu_render_params* p) {
 	return PLU_OK;
 }
 
+// udiv32 for divisor d >= 1 (wavefront.cuh: div_by), checked on the numerators around the multiples of d and at 2^31 - 1
+static udiv32 set_div(uint32_t d) {
+	udiv32 v{d, 0u, 0u};
+	if (d <= 1u) { v.d = 1u; return v; }
+	uint32_t l = 0; while ((1ull << l) < d) ++l;
+	v.m = (uint32_t)(((1ull << (31 + l)) / d) + 1ull); v.sh = l - 1u;
+	const uint32_t probe[] = {0u, d - 1u, d, d + 1u, 2u * d - 1u, 0x7fffffffu / d * d - 1u, 0x7fffffffu / d * d, 0x7fffffffu};
+	for (uint32_t n : probe)
+		if (n <= 0x7fffffffu && (uint32_t)(((unsigned long long)n * v.m) >> 32) >> v.sh != n / d) { std::fprintf(stderr, "plugpu: set_div(%u) fails at %u\n", d, n); std::abort(); }
+	return v;
+}
+
 static wave_desc base_desc(const plu_scene_desc*, const plu_render_params* p, const scene_ref& sc) {
 	wave_desc w{};
 	w.width = p->width; w.height = p->height; w.n_strata = p->n_strata;
+	w.div_width = set_div((uint32_t)p->width); w.div_strata = set_div((uint32_t)p->n_strata);
 	w.sample_begin = p->sample_count > 0 ? p->sample_begin : 0;
 	w.sample_stride = p->sample_count > 0 ? p->sample_stride : 1;
 	w.max_vertices = p->max_vertices > 0 ? p->max_vertices : 8;
@@ -910,7 +923,7 @@ static int render_device_single(plu_gpu_ctx* ctx, const plu_render_params* p, fl
 				}
 				K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, wcap / np));
 				w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
-				w.n_slots = (uint32_t)(np * w.kcount);
+				w.n_slots = (uint32_t)(np * w.kcount); w.div_npix = set_div((uint32_t)np);
 				const int P = (int)(waves % (uint64_t)NP);
 				cudaStream_t sp = ctx->pipe[P];
 				if (waves >= ctx->h_descs_cap) return fail(ctx, PLU_E_NOMEM, "wave descriptor array too small");
@@ -1133,7 +1146,7 @@ extern "C" int plu_gpu_sample_radiance(plu_gpu_ctx* ctx, const plu_render_params
 		int32_t K = (int32_t)std::max<int64_t>(1, std::min<int64_t>(count, ctx->cap[0] / np));
 		for (int32_t k0 = 0; k0 < count; k0 += K) {
 			w.pix0 = (int32_t)p0; w.npix = (int32_t)np; w.k0 = k0; w.kcount = std::min(K, count - k0);
-			w.n_slots = (uint32_t)(np * w.kcount);
+			w.n_slots = (uint32_t)(np * w.kcount); w.div_npix = set_div((uint32_t)np);
 			rc = put_desc(ctx, &w, ctx->stream, 0);   // pageable source: staged before the call returns
 			if (rc != PLU_OK) return rc;
 			enqueue_wave(ctx, sc, w.max_vertices, cfg, ctx->stream);

@@ -1,6 +1,6 @@
 mkdir -p gpurun_out
 ( timeout 600 python -m pytest tests -q -m gpu -x ) > gpurun_out/ab_pytest.log 2>&1; tail -3 gpurun_out/ab_pytest.log
-timeout 300 python bench.py --config cornell-box,room,glass0,synth-boxes --no-cpu-baseline --spp-per-step 256 --steps 6 --warmup 3 2>gpurun_out/ab.err > gpurun_out/ab_bench.jsonl
+timeout 300 python bench.py --config cornell-box,room,glass0,minimal0,synth-boxes --no-cpu-baseline --spp-per-step 256 --steps 6 --warmup 3 2>gpurun_out/ab.err > gpurun_out/ab_bench.jsonl
 python - <<'PY'
 import json
 for l in open("gpurun_out/ab_bench.jsonl"):
