@@ -39,6 +39,7 @@ COMMON = [
     *(["-DPLU_PT_BLOCKS=" + os.environ["PLU_PT_BLOCKS"]] if os.environ.get("PLU_PT_BLOCKS") else []),
     *(["-DPLU_SEED_AREA=" + os.environ["PLU_SEED_AREA"]] if os.environ.get("PLU_SEED_AREA") else []),
     *(["-DPLU_SHADE_BLOCKS=" + os.environ["PLU_SHADE_BLOCKS"]] if os.environ.get("PLU_SHADE_BLOCKS") else []),
+    *(["-DPLU_UNIFORM_UNROLL=" + os.environ["PLU_UNIFORM_UNROLL"]] if os.environ.get("PLU_UNIFORM_UNROLL") else []),
     *(["-DPLU_STAGED_WARP_SCOPE=" + os.environ["PLU_STAGED_WARP_SCOPE"]] if os.environ.get("PLU_STAGED_WARP_SCOPE") else []),
     "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-Xcompiler", "-pthread",
 ]

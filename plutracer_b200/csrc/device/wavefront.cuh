@@ -42,6 +42,7 @@ struct wave_desc {
 	int32_t use_lens;
 	int32_t use_dirty;          // 1: the wave started with k_primary — rad[slot] is only valid where the slot's dirty bit is set
 	udiv32 div_npix, div_width, div_strata;   // divisions by npix, width, n_strata
+	float inv_strata;           // 1.f / (float)n_strata (sampler.h:60; an IEEE division, the same on the host)
 };
 
 struct wave_buffers {
@@ -215,7 +216,7 @@ PLU_DEV ray primary_ray(const scene_ref& sc, const wave_desc& w, uint32_t slot) 
 	slot_to_path(w, slot, key, px_x, px_y, s);
 	u4 o = philox_call(key, 0u);
 	int32_t n = w.n_strata;
-	float dp = 1.f / (float)(uint32_t)n;
+	const float dp = w.inv_strata;
 	const int32_t sq = (int32_t)div_by((uint32_t)s, w.div_strata);
 	float sx = (float)(s - sq * n), sy = (float)sq;
 	f2 px = mk2((float)(uint32_t)px_x + (sx + u01(o.x) * 0.999f) * dp, (float)(uint32_t)px_y + (sy + u01(o.y) * 0.999f) * dp);

@@ -846,6 +846,7 @@ static wave_desc base_desc(const plu_scene_desc*, const plu_render_params* p, co
 	wave_desc w{};
 	w.width = p->width; w.height = p->height; w.n_strata = p->n_strata;
 	w.div_width = set_div((uint32_t)p->width); w.div_strata = set_div((uint32_t)p->n_strata);
+	{ volatile float one = 1.f, nf = (float)(uint32_t)p->n_strata; w.inv_strata = one / nf; }   // (volatile: a division at run time, not a folded constant)
 	w.sample_begin = p->sample_count > 0 ? p->sample_begin : 0;
 	w.sample_stride = p->sample_count > 0 ? p->sample_stride : 1;
 	w.max_vertices = p->max_vertices > 0 ? p->max_vertices : 8;
