@@ -21,7 +21,7 @@
 namespace plud {
 
 #ifndef PLU_STAGED_WARP_SCOPE
-#define PLU_STAGED_WARP_SCOPE 0   // 1: staged-scene kernels push per warp as well (build option; A/B in profiles/r02_summary.md 13)
+#define PLU_STAGED_WARP_SCOPE 0   // bit 0: staged k_extend, bit 1: staged k_shade push per warp as well (build option; A/B in profiles/r02_summary.md 13)
 #endif
 
 // Exact division of a numerator below 2^31 by a wave-uniform divisor: q = umulhi(n, m) >> sh with m = floor(2^(31 + l) / d) + 1,
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(PLU_CTA, 4) k_extend(const __grid_constant__ s
 	// (large scenes: r01f had 34 % of k_extend's stall samples on the CTA barrier, rays of different length).
 	// counts [3] rotate so that the leader can clear one while the warps already add to the next; s_base
 	// is double-buffered for the same reason.
-	constexpr bool WARP_SCOPE = !SMEM || PLU_STAGED_WARP_SCOPE;
+	constexpr bool WARP_SCOPE = !SMEM || (PLU_STAGED_WARP_SCOPE & 1);
 	const uint32_t grp = WARP_SCOPE ? (tid >> 5) : 0u;
 	const bool leader = WARP_SCOPE ? lane == 0 : tid == 0;
 	__shared__ uint32_t s_cnt[PLU_CTA / 32][3][2];
@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(PLU_CTA, PLU_SHADE_BLOCKS) k_shade(const __gri
 	// into shared memory, reserved by ONE thread after the barrier and written in the FOLLOWING iteration;
 	// the shadow payload waits in shared memory meanwhile (st_pay), not in registers.
 	float4* st_pay = (float4*)(stage_base + PLU_STAGE_SHADE_IN);   // [2][5][PLU_CTA]: p|slot, w1|flags, c1, w2, c2
-	constexpr bool WARP_SCOPE = !SMEM || PLU_STAGED_WARP_SCOPE;   // group = CTA for staged scenes, warp otherwise (see k_extend)
+	constexpr bool WARP_SCOPE = !SMEM || (PLU_STAGED_WARP_SCOPE & 2);   // group = CTA for staged scenes, warp otherwise (see k_extend)
 	const uint32_t lane = tid & 31u, grp = WARP_SCOPE ? (tid >> 5) : 0u;
 	const bool leader = WARP_SCOPE ? lane == 0 : tid == 0;
 	__shared__ uint32_t s_sh_cnt[PLU_CTA / 32][3], s_n_cnt[PLU_CTA / 32][3];
