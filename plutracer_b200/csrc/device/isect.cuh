@@ -238,52 +238,95 @@ PLU_DEV bool trace_ref(const scene_ref& sc, const ray& r, float root_bound, floa
 // leaves (a box leaf's node bounds ARE the box, bvh_build.cpp) share one branch-free slab test; a
 // sphere leaf carries (centre, radius) in its node; only triangles fetch primitive data.  Tested
 // surfaces and the tie rule are unchanged.
-// SMEM: the staged nodes are in the paired layout stage_scene(.., pair_nodes = true) leaves — a = (min.x max.x min.y max.y),
-// b = (min.z max.z aux prim) — and the six plane distances are three packed fp32x2 subtract + multiply pairs (sub.rn / mul.rn per
-// half: the scalar results bit for bit, in half the issue slots).
+// One pass of the uniform walk over the PAIRED staged nodes (stage_scene(.., pair_nodes = true): a = (min.x max.x min.y max.y),
+// b = (min.z max.z aux prim)): the six plane distances are three packed fp32x2 subtract + multiply pairs (sub.rn / mul.rn per half:
+// the scalar results bit for bit, in half the issue slots).  EXACT = false: min / max in the IEEE .NaN forms; a box LEAF whose tmin
+// is NaN or zero (a ray that leaves a box starts on one of its planes: about once per secondary ray) is redone on the spot in glm's
+// select order on the same six distances; a NaN at a live INTERIOR node (a direction component of exactly 0 with the origin on a
+// plane of that node's box) is only REPORTED — the caller then repeats the whole walk with EXACT = true (select order at every
+// node), which keeps a compare, a branch and a reconvergence pair out of every interior node of the common pass.
+template <bool COUNT, bool EXACT>
+PLU_DEV bool uniform_pass_paired(const scene_ref& sc, const ref_node* nodes, int32_t n, const ray& r, f3 rrd, float bound,
+                                 float& best_t_out, int32_t& best_out, trace_counts& cnt) {
+	const unsigned long long ex2 = pk2(r.e.x, r.e.x), ey2 = pk2(r.e.y, r.e.y), ez2 = pk2(r.e.z, r.e.z);
+	const unsigned long long ix2 = pk2(rrd.x, rrd.x), iy2 = pk2(rrd.y, rrd.y), iz2 = pk2(rrd.z, rrd.z);
+	float best_t = 0.f; int32_t best = -1;
+	int32_t skip_to = 0;
+	float nan_acc = 0.f;   // NaN once any interior node's tmin was (min.NaN propagates it; a node of a skipped subtree counts too: harmless)
+PLU_UNROLL(PLU_UNIFORM_UNROLL)
+	for (int32_t i = 0; i < n; ++i) {
+		const float4 a = nodes[i].lo, b = nodes[i].hi;
+		const int32_t prim = __float_as_int(b.w), aux = __float_as_int(b.z);   // aux: skip index | surface kind
+		const bool live = i >= skip_to;
+		const bool interior = prim < 0;
+		if (interior || aux == PLU_PRIM_BOX) {
+			float ax, bx, ay, by, az, bz;   // (min - e) * rrd, (max - e) * rrd per axis
+			upk2(submul2(pk2(a.x, a.y), ex2, ix2), ax, bx);
+			upk2(submul2(pk2(a.z, a.w), ey2, iy2), ay, by);
+			upk2(submul2(pk2(b.x, b.y), ez2, iz2), az, bz);
+			float tmin, tmax;
+			if (EXACT) {
+				tmin = gmax(gmax(gmin(ax, bx), gmin(ay, by)), gmin(az, bz));
+				tmax = gmin(gmin(gmax(ax, bx), gmax(ay, by)), gmax(az, bz));
+			} else {
+				tmin = fmax3_nan(fmin_nan(ax, bx), fmin_nan(ay, by), fmin_nan(az, bz));
+				tmax = fmin3_nan(fmax_nan(ax, bx), fmax_nan(ay, by), fmax_nan(az, bz));
+			}
+			if (interior) {
+				if (COUNT && live) cnt.nodes++;
+				if (!EXACT) nan_acc = fmin_nan(nan_acc, tmin);
+				if (live && !(tmax >= tmin)) skip_to = aux;
+			} else {
+				if (!EXACT && ((tmin != tmin) || tmin == 0.f)) {
+					tmin = gmax(gmax(gmin(ax, bx), gmin(ay, by)), gmin(az, bz));
+					tmax = gmin(gmin(gmax(ax, bx), gmax(ay, by)), gmax(az, bz));
+				}
+				if (COUNT && live) cnt.prims++;
+				bool h = !(tmax < tmin || tmin < 0) && !(tmin > bound);
+				if (live && h && (best < 0 || !(best_t < tmin))) { best_t = tmin; best = prim; }
+			}
+		} else {
+			float t; bool h;
+			if (aux == PLU_PRIM_SPHERE) h = sphere_t(make_float4(a.x, a.z, b.x, a.y), r, bound, t);
+			else { const float4* p = sc.prim(prim); h = triangle_t(p[0], p[1], p[2], r, bound, t); }
+			if (COUNT && live) cnt.prims++;
+			if (live && h && (best < 0 || !(best_t < t))) { best_t = t; best = prim; }
+		}
+	}
+	best_t_out = best_t; best_out = best;
+	return nan_acc != nan_acc;
+}
+
+// SMEM: the staged, paired nodes (uniform_pass_paired above); otherwise the table in global memory in its ref_node layout.
 template <bool COUNT, bool SMEM>
 PLU_DEV bool trace_ref_uniform(const scene_ref& sc, const ray& r, float root_bound, float& t_out, int32_t& prim_out, trace_counts* tc) {
 	const ref_node* nodes = sc.ref_nodes();
-	if (SMEM) __builtin_assume(__isShared(nodes));
 	const int32_t n = sc.n_ref_nodes;
 	const f3 rrd = 1.f / r.d;
 	const float bound = n == 1 ? root_bound : PLU_T_MAX;
 	float best_t = 0.f; int32_t best = -1;
-	int32_t skip_to = 0;
-	unsigned long long ex2 = 0, ey2 = 0, ez2 = 0, ix2 = 0, iy2 = 0, iz2 = 0;
 	if (SMEM) {
-		ex2 = pk2(r.e.x, r.e.x); ey2 = pk2(r.e.y, r.e.y); ez2 = pk2(r.e.z, r.e.z);
-		ix2 = pk2(rrd.x, rrd.x); iy2 = pk2(rrd.y, rrd.y); iz2 = pk2(rrd.z, rrd.z);
+		__builtin_assume(__isShared(nodes));
+		trace_counts cnt; cnt.nodes = 0; cnt.prims = 0;
+		if (uniform_pass_paired<COUNT, false>(sc, nodes, n, r, rrd, bound, best_t, best, cnt)) {
+			cnt.nodes = 0; cnt.prims = 0;
+			uniform_pass_paired<COUNT, true>(sc, nodes, n, r, rrd, bound, best_t, best, cnt);
+		}
+		if (COUNT) { tc->nodes += cnt.nodes; tc->prims += cnt.prims; }
+		t_out = best_t; prim_out = best;
+		return best >= 0;
 	}
+	int32_t skip_to = 0;
 PLU_UNROLL(PLU_UNIFORM_UNROLL)
 	for (int32_t i = 0; i < n; ++i) {
-		float4 lo, hi;
-		if (SMEM) {
-			const float4 a = nodes[i].lo, b = nodes[i].hi;
-			lo = make_float4(a.x, a.z, b.x, b.z); hi = make_float4(a.y, a.w, b.y, b.w);   // (only what is used below stays live)
-		} else { lo = nodes[i].lo; hi = nodes[i].hi; }
+		const float4 lo = nodes[i].lo, hi = nodes[i].hi;
 		const int32_t prim = __float_as_int(hi.w), aux = __float_as_int(lo.w);   // aux: skip index | surface kind
 		const bool live = i >= skip_to;
 		const bool interior = prim < 0;
 		if (interior || aux == PLU_PRIM_BOX) {
 			float tmin, tmax;
-			if (SMEM) {
-				float ax, bx, ay, by, az, bz;   // (min - e) * rrd, (max - e) * rrd per axis
-				upk2(submul2(pk2(lo.x, hi.x), ex2, ix2), ax, bx);
-				upk2(submul2(pk2(lo.y, hi.y), ey2, iy2), ay, by);
-				upk2(submul2(pk2(lo.z, hi.z), ez2, iz2), az, bz);
-				tmin = fmax3_nan(fmin_nan(ax, bx), fmin_nan(ay, by), fmin_nan(az, bz));
-				tmax = fmin3_nan(fmax_nan(ax, bx), fmax_nan(ay, by), fmax_nan(az, bz));
-				// hazard (a NaN plane distance; a box hit at distance 0, whose sign is returned): glm's select order on the SAME six
-				// plane distances.  A ray that leaves a box starts on one of its planes, so this is taken about once per secondary ray
-				if ((tmin != tmin) || (!interior && tmin == 0.f)) {
-					tmin = gmax(gmax(gmin(ax, bx), gmin(ay, by)), gmin(az, bz));
-					tmax = gmin(gmin(gmax(ax, bx), gmax(ay, by)), gmax(az, bz));
-				}
-			} else {
-				slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
-				if ((tmin != tmin) || (!interior && tmin == 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);   // hazard: exact glm order
-			}
+			slabs_fast(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);
+			if ((tmin != tmin) || (!interior && tmin == 0.f)) slabs_rrd(mk3(lo), mk3(hi), r.e, rrd, tmin, tmax);   // hazard: exact glm order
 			if (interior) {
 				if (COUNT && live) tc->nodes++;
 				if (live && !(tmax >= tmin)) skip_to = aux;
