@@ -433,3 +433,39 @@ def test_fast_walks_equal_the_reference_tree_on_the_million_surface_scenes(gpu, 
         assert keep.mean() > 0.98 and (x[0] >= 0).mean() > 0.3
         assert differ == 0, out
     record_parity("gpu:synthetic-1M:REF-vs-shipped-walk", out)
+
+
+@pytest.mark.parametrize("name", ["cornell-box", "room", "refrac0"])
+def test_rays_on_interior_node_planes_take_the_exact_walk(gpu, oracle, name):
+    """0 * inf at an INTERIOR node of the reference tree (origin on a plane of the node's box, direction component 0 on that
+    axis): the staged uniform walk only notes the NaN and repeats the walk in glm's select order — same (surface, t) as the
+    CPU oracle, bit for bit, as for every other ray of the batch."""
+    sc = golden_scene(name)
+    gpu.upload(sc)
+    ro, rd = _interior_plane_rays(oracle, sc)
+    assert oracle.nan_slab_rays(sc, ro, rd).mean() > 0.9     # these rays do compute 0 * inf in the reference's boxes
+    ids, t, n = gpu.trace_rays(ro, rd, REF)
+    wi, wt, wn = oracle.trace_rays(sc, ro, rd)
+    assert np.array_equal(ids, wi) and same_bits(t, wt).all() and same_bits(n, wn).all()
+    assert (ids >= 0).any() and (ids < 0).any()
+
+
+def _interior_plane_rays(oracle, sc):
+    lro, b6 = oracle.bvh_nodes(sc)
+    interior = b6[lro[:, 2] < 0]
+    assert len(interior) >= 1
+    rng = np.random.default_rng(17)
+    ro, rd = [], []
+    for nd in interior:
+        lo, hi = nd[0:3], nd[3:6]
+        for axis in range(3):
+            for plane in (lo[axis], hi[axis]):
+                for _ in range(6):
+                    o = (lo + (hi - lo) * rng.uniform(0.05, 0.95, 3)).astype(np.float32)
+                    o[axis] = plane
+                    d = rng.normal(size=3).astype(np.float32)
+                    d[axis] = 0.0
+                    if rng.random() < 0.3:
+                        d[(axis + 1) % 3] = 0.0   # two zero components
+                    ro.append(o); rd.append(d / max(np.linalg.norm(d), 1e-6))
+    return np.array(ro, np.float32), np.array(rd, np.float32)
