@@ -84,3 +84,24 @@ def test_host_memory_entry_points_reject_bad_arguments(lib):
         with pytest.raises(_ffi.PluError):
             texture2d((4, 4), pinned=True)
         assert not texture2d((4, 4), pinned=None).pinned
+
+
+def test_header_is_plain_c_and_links_against_the_library(lib, tmp_path):
+    """include/plugpu.h is the drop-in boundary: it must compile as C99 (no C++ or torch types in the signatures) and a C
+    program must link against libplugpu.so and call a host-side entry point."""
+    import shutil
+    import subprocess
+    from plutracer_b200 import _ffi
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no gcc")
+    src = tmp_path / "c_abi.c"
+    src.write_text('#include <stdio.h>\n#include "plugpu.h"\n'
+                   'int main(void) { plu_scene* s = 0; char err[64]; int rc = plu_scene_load_flat("/nonexistent.pluscene", &s, err, 64);\n'
+                   '  printf("%u %d %lld\\n", plu_abi_version(), rc, (long long)plu_bmp_size(4, 4)); return 0; }\n')
+    exe = tmp_path / "c_abi"
+    libdir = os.path.dirname(_ffi.LIB_PATH)
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                    "-L", libdir, "-l:" + os.path.basename(_ffi.LIB_PATH), "-Wl,-rpath," + libdir], check=True, capture_output=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    assert int(out[0]) == _ffi.ABI_VERSION and int(out[1]) != 0 and int(out[2]) == lib.plu_bmp_size(4, 4)
