@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 namespace pluhost {
 namespace {
@@ -38,9 +39,12 @@ float centroid(const box3& b, int axis) { return (b.mn[axis] + b.mx[axis]) * 1.f
 // (centre, id) pairs: the comparator reads the element itself instead of chasing two tables per comparison
 struct keyed { float k; int32_t v; };
 
-void order_rec(const std::vector<float>* cen, std::vector<int32_t>& s, int axis, std::vector<int32_t>& dfs) {
-	if (s.size() == 1) { dfs.push_back(s[0]); return; }
-	if (s.size() == 2) { dfs.push_back(s[0]); dfs.push_back(s[1]); return; }
+// dfs: where this subtree's leaves go (their DFS positions are a function of the counts alone: the left half comes first).
+// The two halves work on disjoint surfaces and disjoint output ranges, so while `threads_left` allows, the left one runs on a
+// thread of its own — the permutation is the sequential one, std::sort by std::sort.
+void order_rec(const std::vector<float>* cen, std::vector<int32_t>& s, int axis, int32_t* dfs, int threads_left) {
+	if (s.size() == 1) { dfs[0] = s[0]; return; }
+	if (s.size() == 2) { dfs[0] = s[0]; dfs[1] = s[1]; return; }
 	// same std::sort, same comparator outcomes on the same input order as bvh_tree.cpp:23-27 => same permutation
 	std::vector<keyed> kv(s.size());
 	for (size_t i = 0; i < s.size(); ++i) kv[i] = keyed{cen[axis][(size_t)s[i]], s[i]};
@@ -51,8 +55,16 @@ void order_rec(const std::vector<float>* cen, std::vector<int32_t>& s, int axis,
 	for (size_t i = mid; i < s.size(); ++i) rv[i - mid] = kv[i].v;
 	std::vector<keyed>().swap(kv);
 	std::vector<int32_t>().swap(s);
-	order_rec(cen, lv, (axis + 1) % 3, dfs);
-	order_rec(cen, rv, (axis + 1) % 3, dfs);
+	const int next_axis = (axis + 1) % 3;
+	if (threads_left > 1 && lv.size() >= 4096) {
+		const int lt = threads_left / 2;
+		std::thread left([&]() { order_rec(cen, lv, next_axis, dfs, lt); });
+		order_rec(cen, rv, next_axis, dfs + mid, threads_left - lt);
+		left.join();
+	} else {
+		order_rec(cen, lv, next_axis, dfs, 1);
+		order_rec(cen, rv, next_axis, dfs + mid, 1);
+	}
 }
 
 box3 emit_ref(const plu_scene_desc* d, const std::vector<int32_t>& dfs, size_t lo, size_t hi, std::vector<ref_node_h>& out) {
@@ -163,12 +175,11 @@ void reference_leaf_order(const plu_scene_desc* d, std::vector<int32_t>& rank) {
 	size_t n = (size_t)d->n_prims;
 	rank.assign(n, 0);
 	if (n == 0) return;
-	std::vector<int32_t> s(n), dfs;
+	std::vector<int32_t> s(n), dfs(n);
 	for (size_t i = 0; i < n; ++i) s[i] = (int32_t)i;   // load order (scene.h:268-297)
-	dfs.reserve(n);
 	std::vector<float> cen[3];
 	for (int a = 0; a < 3; ++a) { cen[a].resize(n); for (size_t i = 0; i < n; ++i) cen[a][i] = centroid(surface_bounds(d, (int32_t)i), a); }
-	order_rec(cen, s, 0, dfs);
+	order_rec(cen, s, 0, dfs.data(), (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency())));
 	for (size_t k = 0; k < n; ++k) rank[(size_t)dfs[k]] = (int32_t)k;
 }
 

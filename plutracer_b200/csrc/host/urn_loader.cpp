@@ -136,7 +136,7 @@ struct value {
 	value() {}
 	static value integer(int64_t v) { value r; r.type = Int; r.i = v; return r; }
 	static value real(double v) { value r; r.type = Float; r.f = v; return r; }
-	static value block(const value_list& v) { value r; r.type = Block; r.vs = v; return r; }
+	static value block(value_list v) { value r; r.type = Block; r.vs = std::move(v); return r; }   // (callers hand their local list over)
 	static value nativefn(std::function<value()> f) { value r; r.type = Native; r.native = std::make_shared<std::function<value()>>(std::move(f)); return r; }
 
 	bool is_null() const { return type == Null; }
@@ -181,7 +181,7 @@ value parse(token_stream& ts) {
 		if (t.value.empty()) throw parse_error("empty identifier");
 		if (t.value[0] == ':') { v.type = value::Val; v.s = t.value.substr(1); }
 		else if (t.value[0] == '\'') { v.type = value::Id; v.s = t.value.substr(1); }
-		else if (t.value.back() == ':') { v.type = value::Def; v.s = t.value.substr(0, t.value.size() - 1); v.vs = {parse(ts)}; }
+		else if (t.value.back() == ':') { v.type = value::Def; v.s = t.value.substr(0, t.value.size() - 1); v.vs.push_back(parse(ts)); }
 		else { v.type = value::Var; v.s = t.value; }
 	} else {
 		std::string close;
@@ -224,7 +224,7 @@ class eval_context {
 			} else if (v.type == value::Block) out.push_back(format(v.vs, vals));
 			else out.push_back(v);
 		}
-		return value::block(out);
+		return value::block(std::move(out));
 	}
 	// one expression starting at Vs[i]: a function call with its arguments, or a value followed by
 	// any number of `binary-op value` pairs (left to right, no precedence)
@@ -266,7 +266,7 @@ public:
 			if (a.type == value::Int && b.type == value::Float) return value::real((double)a.i + b.f);
 			if (a.type == value::Float && b.type == value::Int) return value::real(a.f + (double)b.i);
 			if (a.type == value::Float && b.type == value::Float) return value::real(a.f + b.f);
-			if (a.type == value::Block && b.type == value::Block) { value_list v = a.vs; v.insert(v.end(), b.vs.begin(), b.vs.end()); return value::block(v); }
+			if (a.type == value::Block && b.type == value::Block) { value_list v = a.vs; v.insert(v.end(), b.vs.begin(), b.vs.end()); return value::block(std::move(v)); }
 			return value();
 		});
 		def_native("do", {"v"}, [this]() { return eval(lookup("v")); });
@@ -283,10 +283,10 @@ public:
 			value_list out;
 			value vs = lookup("vs");
 			for (const auto& b : vs.items()) { const value_list& x = b.items(); out.insert(out.end(), x.begin(), x.end()); }
-			return value::block(out);
+			return value::block(std::move(out));
 		});
 		def_native("append", {"block", "value"}, [this]() -> value {
-			value_list v = lookup("block").items(); v.push_back(lookup("value")); return value::block(v);
+			value_list v = lookup("block").items(); v.push_back(lookup("value")); return value::block(std::move(v));
 		});
 		def_native("collect-range", {"var", "range", "body"}, [this]() -> value {
 			value rng = lookup("range"), body = lookup("body");
@@ -296,7 +296,7 @@ public:
 			value_list out;
 			for (int64_t k = a; k < b; ++k) { bind(id, value::integer(k)); out.push_back(eval(body)); }
 			pop();
-			return value::block(out);
+			return value::block(std::move(out));
 		});
 		def_native("block-format", {"format", "values"}, [this]() -> value {
 			value_list fmt = lookup("format").items();
@@ -336,7 +336,7 @@ public:
 		value_list out;
 		for (size_t i = 0; i < v.vs.size();) out.push_back(expr(v.vs, i));
 		pop();
-		return value::block(out);
+		return value::block(std::move(out));
 	}
 };
 
